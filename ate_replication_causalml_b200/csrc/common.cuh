@@ -1,0 +1,138 @@
+// common.cuh -- internal plumbing shared by the translation units of libate_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/ate_b200.h"
+
+#define ATE_NUM_SMS_FALLBACK 148
+
+struct ate_rng_state {
+    uint32_t mt[624];
+    int mti;
+    bool seeded;
+};
+
+struct ate_ctx {
+    int device = 0;
+    int num_sms = ATE_NUM_SMS_FALLBACK;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    long long launches = 0;
+    // profiling of the dominant kernel (weighted Gram)
+    bool profile = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    double prof_flops = 0.0, prof_bytes = 0.0;
+    long long prof_launches = 0;
+    // small reusable device scratch (block partials, flags)
+    void *scratch = nullptr;
+    size_t scratch_bytes = 0;
+    // gram partial-sum scratch
+    void *gram_scratch = nullptr;
+    size_t gram_scratch_bytes = 0;
+    ate_rng_state rng;
+};
+
+// ---- error handling ------------------------------------------------------------------
+int ate_fail(ate_ctx *ctx, int code, const char *fmt, ...);
+
+#define ATE_CUDA(ctx, call)                                                                   \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            return ate_fail((ctx), -100, "%s:%d: %s -> %s", __FILE__, __LINE__, #call,        \
+                            cudaGetErrorString(e__));                                         \
+    } while (0)
+
+#define ATE_TRY(expr)                 \
+    do {                              \
+        int rc__ = (expr);            \
+        if (rc__ < 0) return rc__;    \
+    } while (0)
+
+#define ATE_LAUNCHED(ctx)                                                                     \
+    do {                                                                                      \
+        (ctx)->launches++;                                                                    \
+        cudaError_t e__ = cudaGetLastError();                                                 \
+        if (e__ != cudaSuccess)                                                               \
+            return ate_fail((ctx), -101, "%s:%d: kernel launch -> %s", __FILE__, __LINE__,    \
+                            cudaGetErrorString(e__));                                         \
+    } while (0)
+
+// ---- RAII device buffer (freed when the entry point returns) ------------------------------
+template <typename T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t n = 0;
+    DevBuf() {}
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+    cudaError_t alloc(size_t count) {
+        release();
+        n = count;
+        return cudaMalloc((void **)&p, sizeof(T) * (count ? count : 1));
+    }
+};
+
+int ate_scratch(ate_ctx *ctx, size_t bytes, void **out);
+int ate_gram_scratch(ate_ctx *ctx, size_t bytes, void **out);
+
+// ---- device helpers ---------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// block-wide sum of NV values per thread; result valid in thread 0 (smem: NV*32 doubles)
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double *smem) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = warp_sum(v[i]);
+    __syncthreads();
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) smem[i * 32 + wid] = v[i];
+    }
+    __syncthreads();
+    if (wid == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            double t = lane < nw ? smem[i * 32 + lane] : 0.0;
+            v[i] = warp_sum(t);
+        }
+    }
+}
+
+// ---- internal entry points used across translation units (device pointers) ---------------
+// row-major design layout: n rows of ld doubles.
+int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t *rows,
+               long long row_begin, long long nrows, const double *v, double *G /*p*p*/);
+int ate_i_transpose_to_rowmajor(ate_ctx *ctx, const double *x_colmajor, long long n, int p,
+                                double *X, long long ld, int col_offset);
+int ate_i_standardize(ate_ctx *ctx, double *d_x, long long n, int p, const int *d_cols, int ncols,
+                      double *d_center, double *d_scale);
+int ate_i_build_design(ate_ctx *ctx, const double *d_xbase, long long n, int p0, int expand,
+                       const double *d_w, const double *d_y, double *d_X, long long ld);
+int ate_i_fill_column(ate_ctx *ctx, double *X, long long n, long long ld, int col, double value);
+int ate_i_score(ate_ctx *ctx, long long n, const double *w, const double *y, const double *p,
+                const double *m0, const double *m1, double *d_est1, double *d_est2,
+                double *tau, double *se);
+int ate_i_bootstrap(ate_ctx *ctx, long long n, const double *d_est1, const double *d_est2, int B,
+                    int mode, const int32_t *d_idx, uint64_t seed, long long rep_offset,
+                    double *boot_host);
+double ate_host_sd(const double *x, long long n);
+void ate_host_rng_seed(ate_rng_state *r, uint32_t seed);
+void ate_host_sample_replace(ate_rng_state *r, int n, long long k, int kind, int32_t *out);
+void ate_host_foldid(ate_rng_state *r, int n, int nfolds, int kind, int32_t *out);

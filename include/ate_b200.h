@@ -1,0 +1,196 @@
+/*
+ * ate_b200.h -- C ABI of libate_b200.so, the B200 (sm_100a) engine for the cross-fitted
+ * AIPW / double-ML ATE path of Zoe187419/ATE_replication_causalML.
+ *
+ * The reference has no FFI of its own: its boundary is the set of R closures that
+ * `source("ate_functions.R")` defines (ate_replication.Rmd:25).  Each entry point below
+ * replaces the native work behind one of those closures (the .Fortran("elnet") /
+ * .Fortran("lognet") cores of glmnet, base R's sample()/mean()/sd(), scale()), and is what a
+ * `.Call` shim binds -- see INTEGRATION.md for the R-side stub of every function.
+ *
+ * Conventions
+ *   - plain C: pointers + sizes, no torch/CUDA types.  `long long` row counts, `int` columns.
+ *   - matrices are column-major doubles exactly as R holds them (`as.matrix(...)`,
+ *     ate_functions.R:94-95,116-117,135-136,299-301); index vectors are 1-based int32 as in R.
+ *   - every function returns 0 on success, <0 on error (ate_last_error(ctx) has the text),
+ *     >0 for glmnet-style non-fatal conditions (e.g. path stopped early at lambda m => -m is
+ *     glmnet's jerr; we return it as +m in `*jerr` fields and 0 as status).
+ *   - a ctx is bound to one GPU; one ctx per thread.  The caller owns every host buffer;
+ *     the library owns device memory inside the ctx.  Nothing outlives ate_ctx_destroy().
+ *   - there is no CPU fallback: without a CUDA device ate_ctx_create() fails.
+ *   - `on_device != 0` (where offered) means the data pointers are device pointers already
+ *     resident on the ctx's GPU (used by bench.py's `value` leg and by multi-GPU drivers).
+ */
+#ifndef ATE_B200_H
+#define ATE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ate_ctx ate_ctx;
+
+#if defined(__GNUC__)
+#define ATE_API __attribute__((visibility("default")))
+#else
+#define ATE_API
+#endif
+
+#define ATE_FAMILY_GAUSSIAN 0
+#define ATE_FAMILY_BINOMIAL 1
+
+#define ATE_BOOT_INDEX 0  /* validation mode: caller supplies the B x n index matrix        */
+#define ATE_BOOT_PHILOX 1 /* production mode: indices drawn on device, Philox4x32-10       */
+
+#define ATE_RNG_ROUNDING 0  /* R <= 3.5 sample(): floor(n * unif_rand())                    */
+#define ATE_RNG_REJECTION 1 /* R >= 3.6 sample(): rejection sampling on ceil(log2 n) bits   */
+
+/* ---- context ------------------------------------------------------------------------- */
+ATE_API int ate_version(void);
+/* No reference counterpart (R's GC owns everything there).  device = CUDA ordinal. */
+ATE_API int ate_ctx_create(int device, ate_ctx **out);
+ATE_API void ate_ctx_destroy(ate_ctx *ctx);
+ATE_API const char *ate_last_error(const ate_ctx *ctx);
+/* Number of kernels this ctx has launched so far (bench.py's `gpu_launches`). */
+ATE_API long long ate_launch_count(const ate_ctx *ctx);
+/* Device time of the dominant kernel (weighted Gram) accumulated since the last reset, from
+ * CUDA events recorded on the ctx stream around each launch: total ms and launch count.
+ * Profiling must be switched on first; off by default. */
+ATE_API int ate_profile_enable(ate_ctx *ctx, int on);
+ATE_API int ate_profile_read(ate_ctx *ctx, double *gram_ms, long long *gram_launches, double *gram_flops,
+                     double *gram_bytes);
+
+/* ---- a1: scale()  (ate_replication.Rmd:72-74) ----------------------------------------- */
+/* In place on x[n*p]: columns `cols` (0-based; NULL = all) get (x-mean)/sd, sd with n-1.
+ * center/scale (length ncols) receive attr(,"scaled:center") / attr(,"scaled:scale"). */
+ATE_API int ate_standardize(ate_ctx *ctx, double *x, long long n, int p, const int *cols, int ncols,
+                    double *center, double *scale);
+
+/* ---- a2: degree-2 expansion  (ate_functions.R:288-296) -------------------------------- */
+/* out[n * (p0*p0 + (include_main ? p0 : 0))], mains first then c1-major ordered products. */
+ATE_API int ate_expand_deg2(ate_ctx *ctx, const double *x, long long n, int p0, int include_main,
+                    double *out);
+
+/* ---- a3/a4: glmnet(x, y, family, alpha = 1, ...)  ------------------------------------- */
+/* Replaces .Fortran("elnet", ...) (ate_functions.R:101-103,123-125,304-305) and
+ * .Fortran("lognet", ...) (ate_functions.R:139-141) together with glmnet()'s R-level
+ * defaults (nlambda 100, lambda.min.ratio 1e-4|1e-2, standardize, intercept, fix.lam).
+ * lambda_in == NULL: automatic sequence.  penalty_factor NULL = ones.  weights are 1.
+ * Outputs: *lmu (<= nlambda), lambda[nlambda], a0[nlambda], beta[p*nlambda] (dense, column l
+ * = coefficients at lambda[l] on the caller's x scale), dev_ratio[nlambda], *npasses,
+ * *nulldev, *jerr (glmnet's jerr). */
+ATE_API int ate_glmnet(ate_ctx *ctx, int family, long long n, int p, const double *x, const double *y,
+               const double *penalty_factor, int nlambda, double lambda_min_ratio,
+               const double *lambda_in, int nlambda_in, double thresh, int maxit, int *lmu,
+               double *lambda, double *a0, double *beta, double *dev_ratio, int *npasses,
+               double *nulldev, int *jerr);
+
+/* ---- cv.glmnet(x, y, alpha = 1, family, penalty.factor)  ------------------------------ */
+/* The wrapper the reference actually calls (same lines).  foldid[n] in 1..nfolds is what
+ * cv.glmnet would draw with sample(rep(seq(nfolds), length = N)); pass it explicitly
+ * (validation mode) or NULL to have it drawn with R's Mersenne-Twister from `seed`
+ * (rng_kind = ATE_RNG_*).  type.measure = "deviance", grouped = TRUE.
+ * idx_min / idx_1se: 0-based positions of lambda.min / lambda.1se. */
+ATE_API int ate_cv_glmnet(ate_ctx *ctx, int family, long long n, int p, const double *x, const double *y,
+                  const double *penalty_factor, int nfolds, const int32_t *foldid, uint32_t seed,
+                  int rng_kind, int nlambda, double thresh, int maxit, int *lmu, double *lambda,
+                  double *a0, double *beta, double *cvm, double *cvsd, int *idx_min, int *idx_1se,
+                  double *dev_ratio, int *jerr);
+
+/* ---- a5: predict(model, newx, type)  (ate_functions.R:144; coef() at :106,:128,:308) --- */
+/* out[n] = a0 + x beta, passed through plogis when response_binomial != 0. */
+ATE_API int ate_predict(ate_ctx *ctx, long long n, int p, const double *x, double a0, const double *beta,
+                int response_binomial, double *out);
+
+/* ---- a7/a8: AIPW score, ATE, sandwich SE  (ate_functions.R:241-243, :255-256) ---------- */
+/* tau = mean(est1, na.rm = TRUE) + mean(est2); se = sqrt(sum(I^2)) / n.  est1/est2 (length n)
+ * are optional outputs (NULL to skip).  on_device: pointers are device pointers. */
+ATE_API int ate_aipw_score(ate_ctx *ctx, long long n, const double *w, const double *y, const double *p,
+                   const double *m0, const double *m1, double *tau, double *se, double *est1,
+                   double *est2, int on_device);
+
+/* ---- a9/a10: bootstrap SE with nuisances held fixed  (ate_functions.R:245-252,267-283) - */
+/* mode ATE_BOOT_INDEX: idx[B*n] (replicate-major, 1-based) is R's sample(n, n, replace = T)
+ * per replicate.  mode ATE_BOOT_PHILOX: indices are drawn on device; replicate b uses the
+ * Philox stream keyed by (seed, rep_offset + b), so a replicate's value does not depend on how
+ * replicates are sharded over GPUs.  boot[B] receives the replicate estimates and *se their
+ * sd (n-1 denominator) -- pass se = NULL when sharding and combine boot[] yourself. */
+ATE_API int ate_bootstrap(ate_ctx *ctx, long long n, const double *w, const double *y, const double *p,
+                  const double *m0, const double *m1, int B, int mode, const int32_t *idx,
+                  uint64_t seed, long long rep_offset, double *boot, double *se, int on_device);
+
+/* One replicate, the literal tau_hat_dr_est(w, y, p, tauhat0x, tauhat1x) of :267-283 with the
+ * index vector that sample() would have produced. */
+ATE_API int ate_tau_hat_dr_est(ate_ctx *ctx, long long n, const double *w, const double *y,
+                       const double *p, const double *m0, const double *m1, const int32_t *idx,
+                       double *tau);
+
+/* ---- f1: R's sample() on the host, bit-exact with set.seed(seed)  (ate_functions.R:269) - */
+/* state lives in the ctx.  ate_r_sample: k draws of sample(n, k, replace = TRUE) (1-based).
+ * ate_r_foldid: sample(rep(seq(nfolds), length = n)). */
+ATE_API int ate_r_set_seed(ate_ctx *ctx, uint32_t seed);
+ATE_API int ate_r_sample(ate_ctx *ctx, int n, long long k, int rng_kind, int32_t *out);
+ATE_API int ate_r_foldid(ate_ctx *ctx, int n, int nfolds, int rng_kind, int32_t *out);
+
+/* ---- the composite: K-fold cross-fitted AIPW with glmnet nuisances --- */
+typedef struct ate_crossfit_opts {
+    int K;              /* outer folds (default 5)                                            */
+    int nfolds_inner;   /* cv.glmnet nfolds inside each training set (default 10)             */
+    int nlambda;        /* default 100                                                        */
+    double thresh;      /* default 1e-7                                                       */
+    int maxit;          /* default 100000                                                     */
+    int use_1se;        /* 1: lambda.1se (the reference's default `s`), 0: lambda.min         */
+    int standardize_base; /* 1: scale() the first n_continuous base columns first (a1)       */
+    int n_continuous;
+    int expand;         /* 0: design = base columns; 1: products only (p0^2);                 */
+                        /* 2: mains + products (what belloni() literally builds)              */
+    int B;              /* bootstrap replicates (0 = none)                                    */
+    int boot_mode;      /* ATE_BOOT_*                                                         */
+    uint64_t boot_seed;
+    long long boot_rep_offset; /* first replicate id handled by this call (GPU sharding)      */
+    int boot_reps_here; /* replicates computed by this call (<= B; 0 = all B)                 */
+    uint32_t r_seed;    /* seed for fold ids when foldid / inner ids are NULL                 */
+    int rng_kind;       /* ATE_RNG_*                                                          */
+    int on_device;      /* x_base, w, y are device pointers                                   */
+    int fold_begin;     /* outer folds [fold_begin, fold_end) fitted by this call (1-based,   */
+    int fold_end;       /*   0,0 = all); rows of other folds get NaN nuisances                */
+    int skip_score;     /* 1: stop after the nuisances (multi-GPU drivers combine first)      */
+} ate_crossfit_opts;
+
+ATE_API void ate_crossfit_default_opts(ate_crossfit_opts *o);
+
+typedef struct ate_crossfit_result {
+    double tau, se_sandwich, se_bootstrap, lower_ci, upper_ci; /* a11: tau +- 1.96 se          */
+    int jerr;              /* worst glmnet jerr met                                           */
+    int rounds_irls;       /* lock-step IRLS rounds executed                                  */
+    long long gram_launches;
+    double ms_design, ms_outcome, ms_propensity, ms_score, ms_bootstrap; /* host wall, synced */
+} ate_crossfit_result;
+
+/* x_base[n*p0] col-major, w[n], y[n].  foldid[n] (1..K) and inner_ps / inner_out [K*n]
+ * (row k: cv.glmnet fold ids of outer fold k's training rows in training-row order) may be
+ * NULL => drawn with R's RNG from opts->r_seed in the order R would (k = 1..K: propensity
+ * cv.glmnet then outcome cv.glmnet).  boot_idx: B*n for ATE_BOOT_INDEX, else NULL.
+ * Outputs (host, may be NULL): phat, m0, m1 [n] stitched out-of-fold nuisances;
+ * lambda_ps, lambda_out [K]; boot [B]. */
+ATE_API int ate_crossfit_aipw(ate_ctx *ctx, const ate_crossfit_opts *opts, long long n, int p0,
+                      const double *x_base, const double *w, const double *y,
+                      const int32_t *foldid, const int32_t *inner_ps, const int32_t *inner_out,
+                      const int32_t *boot_idx, double *phat, double *m0, double *m1,
+                      double *lambda_ps, double *lambda_out, double *boot,
+                      ate_crossfit_result *res);
+
+/* ---- weighted Gram, exposed for tests, roofline measurement and multi-GPU drivers ------ */
+/* x: n x p col-major host matrix (or, with on_device, the library's row-major device layout:
+ * n rows of ld doubles, ld % 2 == 0).  G[p*p] = sum_i v_i x_i x_i^T (v NULL = 1), both
+ * triangles filled.  Rows are taken from rows[nrows] (0-based; NULL = all n rows). */
+ATE_API int ate_weighted_gram(ate_ctx *ctx, long long n, int p, const double *x, long long ld,
+                      const double *v, const int32_t *rows, long long nrows, double *G,
+                      int on_device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ATE_B200_H */
