@@ -1,0 +1,166 @@
+"""Host-side mirror of the reference's R entry points (`/root/reference/ate_functions.R`).
+
+R is not installed in this image, so the closures a maintainer would keep in `ate_functions.R`
+(see INTEGRATION.md for the `.Call` versions) are mirrored here in Python with the same names,
+argument meaning, return shape (`Method, ATE, lower_ci, upper_ci`) and quirks:
+
+* like the R code, the lasso estimators read the module-level global ``covariates``
+  (ate_functions.R:91,113,135,289) -- set it with ``set_covariates([...])``;
+* ``coef(model)`` / ``predict(model)`` on a cv.glmnet object use ``s = "lambda.1se"``
+  (ate_functions.R:106,128,144); ``belloni`` evaluates BOTH models at ``model_xw$lambda.min``
+  (:308-309), keeps only positive coefficients (:312-313) and shifts the union by one (:314);
+* ``doubly_robust_glm`` hard-codes ``B <- 1000`` (:247) -- kept as the default of a new
+  trailing argument.
+
+All numerical work goes through the C ABI (``Engine``); nothing here falls back to the CPU.
+``dataset`` is a pandas DataFrame (the stand-in for R's data.frame).
+"""
+from __future__ import annotations
+
+import numpy as np
+import pandas as pd
+
+from .engine import Engine, RNG_REJECTION
+
+covariates: list[str] = []
+_engine: Engine | None = None
+
+
+def set_covariates(names):
+    global covariates
+    covariates = list(names)
+
+
+def engine() -> Engine:
+    global _engine
+    if _engine is None:
+        _engine = Engine(0)
+    return _engine
+
+
+def set_engine(e: Engine):
+    global _engine
+    _engine = e
+
+
+def _row(method, tau_hat, lower_ci, upper_ci):
+    return pd.DataFrame({"Method": [method], "ATE": [tau_hat], "lower_ci": [lower_ci],
+                         "upper_ci": [upper_ci]})
+
+
+# ---------------------------------------------------------------- ate_functions.R:89-108
+def ate_condmean_lasso(dataset, treatment_var, outcome_var, foldid=None, seed=None):
+    regs = list(covariates) + [treatment_var]
+    x = dataset[regs].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    pfac = np.r_[np.ones(len(covariates)), 0.0]          # :98
+    model = engine().cv_glmnet(x, y, "gaussian", penalty_factor=pfac, foldid=foldid,
+                               seed=0 if seed is None else seed)
+    betaw = float(model["beta"][len(covariates), model["idx_1se"]])  # coef(model)[treatment_var,]
+    return _row("Single-equation LASSO", betaw, betaw, betaw)
+
+
+# ---------------------------------------------------------------- ate_functions.R:111-130
+def ate_lasso(dataset, treatment_var, outcome_var, foldid=None, seed=None):
+    regs = list(covariates) + [treatment_var]
+    x = dataset[regs].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    pfac = np.r_[np.ones(len(covariates)), 1.0]          # :120
+    model = engine().cv_glmnet(x, y, "gaussian", penalty_factor=pfac, foldid=foldid,
+                               seed=0 if seed is None else seed)
+    betaw = float(model["beta"][len(covariates), model["idx_1se"]])
+    return _row("Usual LASSO", betaw, betaw, betaw)
+
+
+# ---------------------------------------------------------------- ate_functions.R:133-146
+def prop_score_lasso(dataset, treatment_var, foldid=None, seed=None):
+    """Returns an n x 1 matrix, as predict(cv.glmnet, type = "response") does."""
+    x = dataset[list(covariates)].to_numpy(dtype=np.float64)
+    w = dataset[treatment_var].to_numpy(dtype=np.float64)
+    model = engine().cv_glmnet(x, w, "binomial", foldid=foldid, seed=0 if seed is None else seed)
+    s = model["idx_1se"]
+    p = engine().predict(x, model["a0"][s], model["beta"][:, s], response_binomial=True)
+    return p.reshape(-1, 1)
+
+
+# ---------------------------------------------------------------- ate_functions.R:267-283
+def tau_hat_dr_est(w, y, p, tauhat0x, tauhat1x, bootstrap_sample_idx=None):
+    """One bootstrap replicate.  The R function draws sample(length(w), length(w), replace = T)
+    from the global RNG; pass that vector (1-based), or None to draw it with the engine's
+    R-compatible Mersenne-Twister stream (Engine.r_set_seed)."""
+    w = np.asarray(w, dtype=np.float64)
+    if bootstrap_sample_idx is None:
+        bootstrap_sample_idx = engine().r_sample(w.size, w.size, RNG_REJECTION)
+    return engine().tau_hat_dr_est(w, y, p, tauhat0x, tauhat1x, bootstrap_sample_idx)
+
+
+# ---------------------------------------------------------------- ate_functions.R:241-263
+def doubly_robust_scores(w, y, p, tauhat0x, tauhat1x, bootstrap_se=False, B=1000, boot_idx=None,
+                         boot_seed=1991, method="Doubly Robust"):
+    """Lines :241-263 of doubly_robust_glm for given nuisance vectors: AIPW point estimate,
+    sandwich or bootstrap SE, +-1.96 se interval."""
+    tau_hat, se_sand = engine().aipw_score(w, y, p, tauhat0x, tauhat1x)
+    if bootstrap_se:
+        se_hat, _ = engine().bootstrap(w, y, p, tauhat0x, tauhat1x, B=B, idx=boot_idx, seed=boot_seed)
+    else:
+        se_hat = se_sand
+    return _row(method, tau_hat, tau_hat - se_hat * 1.96, tau_hat + se_hat * 1.96)
+
+
+def crossfit_aipw(dataset, treatment_var, outcome_var, bootstrap_se=True, B=1000, K=5, seed=1991,
+                  foldid=None, inner_ps=None, inner_out=None, boot_idx=None, expand=0,
+                  n_continuous=0, use_1se=True, method="Cross-fitted AIPW with glmnet nuisances"):
+    """The composite of SURVEY.md section 8: K-fold cross-fitted doubly-robust ATE with
+    L1-logistic propensity (:139-141) and lasso outcome (:98-103) nuisances, AIPW score
+    (:241-243), sandwich (:255-256) or bootstrap (:245-252) SE, interval (:260-263)."""
+    x = dataset[list(covariates)].to_numpy(dtype=np.float64)
+    w = dataset[treatment_var].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    r = engine().crossfit_aipw(x, w, y, foldid=foldid, inner_ps=inner_ps, inner_out=inner_out,
+                               boot_idx=boot_idx, K=K, B=B if bootstrap_se else 0,
+                               boot_mode=0 if boot_idx is not None else 1, boot_seed=seed, r_seed=seed,
+                               expand=expand, n_continuous=n_continuous,
+                               standardize_base=int(n_continuous > 0), use_1se=int(use_1se))
+    se = r["se_bootstrap"] if bootstrap_se else r["se_sandwich"]
+    out = _row(method, r["tau"], r["tau"] - 1.96 * se, r["tau"] + 1.96 * se)
+    out.attrs["detail"] = r
+    return out
+
+
+# ---------------------------------------------------------------- ate_functions.R:286-328
+def belloni_selection(dataset, treatment_var, outcome_var, foldid_xw=None, foldid_xy=None, seed=None):
+    """belloni() up to the post-lasso OLS (which SURVEY.md ranks as the next row, f4): the
+    expansion (:288-296), the two gaussian cv.glmnet fits (:304-305), coefficients at
+    model_xw$lambda.min for BOTH models (:308-309) and the selected support with the
+    reference's `> 0` and `- 1` quirks (:312-314).  Returns (c_union, x_expanded)."""
+    x0 = dataset[list(covariates)].to_numpy(dtype=np.float64)
+    x = engine().expand_deg2(x0, include_main=True)
+    w = dataset[treatment_var].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    model_xw = engine().cv_glmnet(x, w, "gaussian", foldid=foldid_xw, seed=0 if seed is None else seed)
+    model_xy = engine().cv_glmnet(x, y, "gaussian", foldid=foldid_xy, seed=0 if seed is None else seed + 1)
+    s = model_xw["lambda_min"]
+    c_xw = model_xw["beta"][:, model_xw["idx_min"]]
+    c_xy = _coef_at(model_xy, s)
+    nz_xw = np.nonzero(c_xw > 0)[0] + 1       # which(), 1-based
+    nz_xy = np.nonzero(c_xy > 0)[0] + 1
+    c_union = pd.unique(np.r_[nz_xw, nz_xy]) - 1
+    c_union = c_union[c_union > 0]            # x[, 0] is silently dropped by R
+    return c_union, x
+
+
+def _coef_at(model, s):
+    """coef(glmnet.fit, s = s): linear interpolation in lambda (lambda.interp)."""
+    lam = model["lambda_"]
+    if s >= lam[0]:
+        return model["beta"][:, 0]
+    if s <= lam[-1]:
+        return model["beta"][:, -1]
+    sfrac = (lam[0] - s) / (lam[0] - lam[-1])
+    lamf = (lam[0] - lam) / (lam[0] - lam[-1])
+    coord = np.interp(sfrac, lamf, np.arange(lam.size))
+    left, right = int(np.floor(coord)), int(np.ceil(coord))
+    if left == right:
+        return model["beta"][:, left]
+    f = (sfrac - lamf[right]) / (lamf[left] - lamf[right])
+    return model["beta"][:, left] * f + model["beta"][:, right] * (1 - f)

@@ -82,8 +82,9 @@ __device__ __forceinline__ void block_coords(int q, int &bi, int &bj) {
 
 __global__ void __launch_bounds__(G_THREADS, 1)
 gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const int32_t *__restrict__ rows,
-                 long long row_begin, long long nrows, long long rows_per_chunk,
-                 const double *__restrict__ v, int nblk, int stages, double *__restrict__ partials) {
+                 long long row_begin, long long nrows, long long hole_begin, long long hole_len,
+                 long long rows_per_chunk, const double *__restrict__ v, int nblk, int stages,
+                 double *__restrict__ partials) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int pitch = ncols + G_PAD;                       // doubles
     const size_t stage_doubles = (size_t)G_ROWS * pitch;
@@ -126,7 +127,9 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
             if (lane == 0) mbar_arrive_expect_tx(full + s, row_bytes * (uint32_t)__popc(vmask));
             __syncwarp();
             if (valid) {
-                const long long r = rows ? (long long)__ldg(rows + row_begin + t) : row_begin + t;
+                // logical position t skips the hole (the held-out inner fold of a CV fit)
+                const long long tp = row_begin + t + (t >= hole_begin ? hole_len : 0);
+                const long long r = rows ? (long long)__ldg(rows + tp) : tp;
                 bulk_g2s(dst, X + (size_t)r * (size_t)ld, row_bytes, full + s);
             }
         }
@@ -203,9 +206,15 @@ __global__ void gram_fold_kernel(const double *__restrict__ partials, int nchunk
 
 // X: row-major device design (ld doubles per row; columns [0, round_up(p,32)) must be readable
 // and zero beyond the real columns).  rows: device row list or NULL.  v: device weights indexed
-// by position in the list (or NULL).  G: device p*p output.
+// by position in the list (or NULL).  G: device p*p output.  The nrows logical positions map to
+// list entries row_begin + t, skipping hole_len entries from logical position hole_begin on.
 int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t *rows,
-               long long row_begin, long long nrows, const double *v, double *G) {
+               long long row_begin, long long nrows, const double *v, double *G, long long hole_begin,
+               long long hole_len) {
+    if (hole_len <= 0) {
+        hole_begin = nrows;
+        hole_len = 0;
+    }
     if (p <= 0 || nrows < 0) return ate_fail(ctx, -1, "gram: bad shape");
     const int ncols = (p + 31) / 32 * 32;
     if (ncols > ld) return ate_fail(ctx, -1, "gram: ld (%lld) < padded column count (%d)", ld, ncols);
@@ -242,7 +251,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
         ATE_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     }
     gram_dmma_kernel<<<dim3(ngroups, nchunks), G_THREADS, smem, ctx->stream>>>(
-        X, ld, ncols, rows, row_begin, nrows, rpc, v, nblk, stages, (double *)scr);
+        X, ld, ncols, rows, row_begin, nrows, hole_begin, hole_len, rpc, v, nblk, stages, (double *)scr);
     ATE_LAUNCHED(ctx);
     if (ctx->profile) {
         ATE_CUDA(ctx, cudaEventRecord(e1, ctx->stream));

@@ -1,0 +1,869 @@
+// path_binom.cu -- a4: L1-logistic path + cv.glmnet (ate_functions.R:139-141 -> glmnet's
+// lognet, two-class Newton) as lock-step IRLS rounds in Gram space.
+//
+// glmnet's lognet2n touches the n observations in three places per IRLS step: the curvature
+// xv_j = sum v x_j^2, the coordinate gradients g_k = <r, x_k> inside the coordinate-descent
+// sweeps (O(n) each), and the refresh of (q, v, r).  Here every O(n) piece of one IRLS step
+// is done by two passes:
+//   lognet_eval_kernel : eta = a0 + x beta, q = plogis(eta) (glmnet's clamping), v = w q (1-q),
+//                        r = w (y - q); plus sum v, sum r, deviance, X^T r and X^T v.
+//                        One warp per observation row, rows read once (HBM-bound).
+//   gram.cu            : H = X^T V X on the DMMA pipe (tensor-bound, the dominant cost).
+// and the coordinate descent then runs on the p x p quadratic:
+//   lognet_cd_kernel   : one CTA per fit.  Standardises H in place (lstandard1's centring and
+//                        1/N scaling are affine in H, X^T v, sum v), then follows lognet2n's
+//                        loop order exactly -- strong-set sweep, intercept step, active-set
+//                        loop -- with g_k = <r, x_k> kept current by covariance updates
+//                        g -= d * H[:,k].  In exact arithmetic the iterates equal glmnet's.
+// All fits of a batch (the full-data fits of every outer fold, then all their CV folds) advance
+// one IRLS step per round; finished fits drop out.  The host reads one small flag vector per
+// round.
+#include <math.h>
+
+#include "path.cuh"
+
+namespace {
+
+enum { PH_INIT = 0, PH_REFRESH = 1 };
+enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_N };
+enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_N };
+// sums layout: gr[ni], hx[ni], then XMZ, SR, DEV
+enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
+
+struct LognetFit {
+    const int32_t *list;  // row ids (NULL = identity)
+    long long nt, hole_begin, hole_len;
+    int ni, iy;
+    const double *vp;
+    double flmin;
+    const double *ulam;
+    const int *nlam_ptr;
+    int nlam;
+    double thr;
+    int maxit;
+    double *v, *r;    // [nt]
+    double *H;        // ni x ni
+    double *sums;     // 2 ni + SU_N
+    double *coef;     // ni + 1 (a0 last): raw-scale coefficients for the next eval
+    double *st_d;     // b, bs, xv, ga, xm, xs, vq [7 ni] + SD_N
+    int *st_i;        // ixx, mm, mlist, ju [4 ni] + SI_N
+    double *alm, *a0, *dev, *beta;  // outputs
+};
+
+constexpr int EV_THREADS = 256;
+constexpr int CD_THREADS = 256;
+
+__device__ __forceinline__ long long phys_pos(const LognetFit &f, long long t) {
+    return t + (t >= f.hole_begin ? f.hole_len : 0);
+}
+
+// ---- per-row pass -------------------------------------------------------------------------
+template <int ITER>
+__global__ void __launch_bounds__(EV_THREADS)
+lognet_eval_kernel(const LognetFit *__restrict__ fits, int fid, const double *__restrict__ X,
+                   long long ld, double *__restrict__ partials) {
+    const LognetFit f = fits[fid];
+    extern __shared__ double sm[];  // [warps][2*ni + SU_N]
+    const int ni = f.ni;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int plen = 2 * ni + SU_N;
+    double beta[2 * ITER], gr[2 * ITER], hx[2 * ITER];
+#pragma unroll
+    for (int i = 0; i < ITER; ++i) {
+        const int c = 2 * lane + 64 * i;
+        beta[2 * i] = c < ni ? f.coef[c] : 0.0;
+        beta[2 * i + 1] = c + 1 < ni ? f.coef[c + 1] : 0.0;
+        gr[2 * i] = gr[2 * i + 1] = hx[2 * i] = hx[2 * i + 1] = 0.0;
+    }
+    const double a0 = f.coef[ni];
+    const double w = 1.0 / (double)f.nt;
+    const double pmin = GLM_PMIN, fmax_ = log(1.0 / pmin - 1.0), fmin_ = -fmax_;
+    double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0;
+    const long long wstride = (long long)gridDim.x * nw;
+    for (long long t = (long long)blockIdx.x * nw + wid; t < f.nt; t += wstride) {
+        const long long pp = phys_pos(f, t);
+        const long long row = f.list ? (long long)__ldg(f.list + pp) : pp;
+        const double *xr = X + (size_t)row * (size_t)ld;
+        double x[2 * ITER];
+        double dot = 0.0;
+#pragma unroll
+        for (int i = 0; i < ITER; ++i) {
+            const int c = 2 * lane + 64 * i;
+            double2 t2 = make_double2(0.0, 0.0);
+            if (c + 1 < ld) t2 = __ldg(reinterpret_cast<const double2 *>(xr + c));
+            x[2 * i] = t2.x;
+            x[2 * i + 1] = t2.y;
+            dot += t2.x * beta[2 * i] + t2.y * beta[2 * i + 1];
+        }
+        const double yi = __ldg(xr + f.iy);
+        const double fi = a0 + warp_sum(dot);
+        double q;
+        if (fi < fmin_)
+            q = 0.0;
+        else if (fi > fmax_)
+            q = 1.0;
+        else
+            q = 1.0 / (1.0 + exp(-fi));
+        const double vi = w * q * (1.0 - q), ri = w * (yi - q);
+        if (lane == 0) {
+            f.v[t] = vi;
+            f.r[t] = ri;
+            const double qc = fmin(fmax(q, pmin), 1.0 - pmin);
+            s_xmz += vi;
+            s_sr += ri;
+            s_dev -= w * (yi * log(qc) + (1.0 - yi) * log(1.0 - qc));
+        }
+#pragma unroll
+        for (int i = 0; i < 2 * ITER; ++i) {
+            gr[i] += ri * x[i];
+            hx[i] += vi * x[i];
+        }
+    }
+    double *mine = sm + (size_t)wid * plen;
+#pragma unroll
+    for (int i = 0; i < ITER; ++i) {
+        const int c = 2 * lane + 64 * i;
+        if (c < ni) {
+            mine[c] = gr[2 * i];
+            mine[ni + c] = hx[2 * i];
+        }
+        if (c + 1 < ni) {
+            mine[c + 1] = gr[2 * i + 1];
+            mine[ni + c + 1] = hx[2 * i + 1];
+        }
+    }
+    if (lane == 0) {
+        mine[2 * ni + SU_XMZ] = s_xmz;
+        mine[2 * ni + SU_SR] = s_sr;
+        mine[2 * ni + SU_DEV] = s_dev;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < plen; e += blockDim.x) {
+        double s = 0.0;
+        for (int q = 0; q < nw; ++q) s += sm[(size_t)q * plen + e];
+        partials[(size_t)blockIdx.x * plen + e] = s;
+    }
+}
+
+__global__ void fold_partials_kernel(const double *__restrict__ partials, int nparts, int len,
+                                     double *__restrict__ out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= len) return;
+    double s = 0.0;
+    for (int q = 0; q < nparts; ++q) s += partials[(size_t)q * len + e];
+    out[e] = s;
+}
+
+// sum of the response column over the fit's rows -> q0, bz; arms the first eval
+__global__ void __launch_bounds__(256)
+lognet_init_kernel(const LognetFit *__restrict__ fits, const double *__restrict__ X, long long ld) {
+    const LognetFit f = fits[blockIdx.x];
+    __shared__ double red[32];
+    double acc[1] = {0.0};
+    for (long long t = threadIdx.x; t < f.nt; t += blockDim.x) {
+        const long long pp = phys_pos(f, t);
+        const long long row = f.list ? (long long)__ldg(f.list + pp) : pp;
+        acc[0] += __ldg(X + (size_t)row * (size_t)ld + f.iy);
+    }
+    block_sum<1>(acc, red);
+    for (int j = threadIdx.x; j < f.ni; j += blockDim.x) f.coef[j] = 0.0;
+    if (threadIdx.x == 0) {
+        const double q0 = acc[0] / (double)f.nt;
+        const double bz = log(q0 / (1.0 - q0));
+        f.coef[f.ni] = bz;
+        double *sd = f.st_d + 7 * (size_t)f.ni;
+        int *si = f.st_i + 4 * (size_t)f.ni;
+        for (int k = 0; k < SD_N; ++k) sd[k] = 0.0;
+        for (int k = 0; k < SI_N; ++k) si[k] = 0;
+        sd[SD_Q0] = q0;
+        sd[SD_BZ] = bz;
+        sd[SD_B0] = bz;
+        si[SI_PHASE] = PH_INIT;
+        if (q0 <= GLM_PMIN) {
+            si[SI_JERR] = 8001;
+            si[SI_DONE] = 1;
+        } else if (q0 >= 1.0 - GLM_PMIN) {
+            si[SI_JERR] = 9001;
+            si[SI_DONE] = 1;
+        }
+    }
+}
+
+__device__ __forceinline__ double bsum_all(double v, double *red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[wid] = v;
+    __syncthreads();
+    double t = 0.0;
+    for (int i = 0; i < nw; ++i) t += red[i];
+    __syncthreads();
+    return t;
+}
+__device__ __forceinline__ double bmax_all(double v, double *red) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    __syncthreads();
+    if (lane == 0) red[wid] = v;
+    __syncthreads();
+    double t = red[0];
+    for (int i = 1; i < nw; ++i) t = fmax(t, red[i]);
+    __syncthreads();
+    return t;
+}
+
+// ---- one IRLS round of coordinate descent per fit -------------------------------------------
+__global__ void __launch_bounds__(CD_THREADS)
+lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flags) {
+    const LognetFit f = fits[blockIdx.x];
+    const int ni = f.ni, tid = threadIdx.x, T = blockDim.x;
+    int *si = f.st_i + 4 * (size_t)ni;
+    double *sd = f.st_d + 7 * (size_t)ni;
+    if (si[SI_DONE]) {
+        if (tid == 0) done_flags[blockIdx.x] = 1;
+        return;
+    }
+    extern __shared__ double sm[];
+    double *b = sm, *g = b + ni, *hxs = g + ni, *xv = hxs + ni, *vq = xv + ni, *red = vq + ni;  // red[32]
+    int *ixx = reinterpret_cast<int *>(red + 32), *mm = ixx + ni, *ml = mm + ni, *ju = ml + ni;
+    double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gga = Gxv + ni, *Gxm = Gga + ni,
+           *Gxs = Gxm + ni, *Gvq = Gxs + ni;
+    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni;
+    double *H = f.H;
+    const double *gr = f.sums, *hx = f.sums + ni;
+    const double xmz = f.sums[2 * ni + SU_XMZ], sr_in = f.sums[2 * ni + SU_SR];
+    const double devsum = f.sums[2 * ni + SU_DEV];
+    const double pmin = GLM_PMIN, vmin = (1.0 + pmin) * pmin * (1.0 - pmin);
+
+    int nin = si[SI_NIN], ilm = si[SI_ILM], nlp = si[SI_NLP];
+    const int phase = si[SI_PHASE];
+    double b0 = sd[SD_B0], al = sd[SD_AL], al0 = sd[SD_AL0];
+    const int nlam = (f.flmin < 1.0) ? f.nlam : min(f.nlam, *f.nlam_ptr);
+    const int mnl = min(GLM_MNLAM, nlam);
+
+    if (phase == PH_INIT) {
+        // lstandard1 from the first pass (v = w q0 (1 - q0) is constant there)
+        double vs = 0.0;
+        for (int j = tid; j < ni; j += T) {
+            const double m = hx[j] / xmz;
+            const double sq = H[(size_t)j * ni + j] / xmz;
+            const double var = sq - m * m;
+            const bool ok = var > 1.0e-14 * (sq > 1.0e-300 ? sq : 1.0e-300);
+            Gxm[j] = m;
+            Gxs[j] = ok ? sqrt(var) : 1.0;
+            Gju[j] = ok ? 1 : 0;
+            const double t = f.vp ? fmax(f.vp[j], 0.0) : 1.0;
+            Gvq[j] = t;
+            vs += t;
+            Gb[j] = 0.0;
+            Gbs[j] = 0.0;
+            Gxv[j] = 0.0;
+            Gixx[j] = 0;
+            Gmm[j] = 0;
+            Gml[j] = 0;
+        }
+        vs = bsum_all(vs, red);
+        for (int j = tid; j < ni; j += T) Gvq[j] = Gvq[j] * (double)ni / vs;
+        __syncthreads();
+    }
+    // ---- state into shared memory; standardise this round's moments ----
+    for (int j = tid; j < ni; j += T) {
+        b[j] = Gb[j];
+        vq[j] = Gvq[j];
+        ixx[j] = Gixx[j];
+        mm[j] = Gmm[j];
+        ml[j] = Gml[j];
+        ju[j] = Gju[j];
+        const double m = Gxm[j], s = Gxs[j];
+        g[j] = ju[j] ? (gr[j] - m * sr_in) / s : 0.0;
+        hxs[j] = ju[j] ? (hx[j] - m * xmz) / s : 0.0;
+    }
+    __syncthreads();
+    for (int e = tid; e < ni * ni; e += T) {
+        const int r = e / ni, c = e - r * ni;
+        const double mr = Gxm[r], mc = Gxm[c];
+        H[e] = (H[e] - mr * hx[c] - mc * hx[r] + mr * mc * xmz) / (Gxs[r] * Gxs[c]);
+    }
+    __syncthreads();
+    double sr = sr_in;
+    double dev0 = sd[SD_DEV0], dev1 = sd[SD_DEV1], shr = sd[SD_SHR], alf = sd[SD_ALF];
+    bool begin_lambda = false, finished = false;
+    int jerr = 0;
+
+    if (phase == PH_INIT) {
+        const double q0 = sd[SD_Q0], bz = sd[SD_BZ];
+        dev1 = -(bz * q0 + log(1.0 - q0));
+        dev0 = dev1;  // y is 0/1: the y log y terms vanish
+        shr = f.thr * dev0;
+        alf = (f.flmin < 1.0) ? pow(fmax(GLM_EPS, f.flmin), 1.0 / (double)(nlam - 1)) : 1.0;
+        for (int j = tid; j < ni; j += T) Gga[j] = ju[j] ? fabs(g[j]) : 0.0;
+        __syncthreads();
+        ilm = 0;
+        al = 0.0;
+        begin_lambda = true;
+    } else {
+        // ---- the quadratic was just refreshed at the new coefficients: converged? ----
+        bool stop_path = (xmz <= vmin);
+        bool again = false;
+        if (!stop_path) {
+            const double d0 = b0 - sd[SD_BS0];
+            int moved = (xmz * d0 * d0 >= shr) ? 1 : 0;
+            for (int l = tid; l < nin; l += T) {
+                const int k = ml[l];
+                const double d = b[k] - Gbs[k];
+                if (Gxv[k] * d * d >= shr) moved = 1;
+            }
+            moved = __syncthreads_or(moved);
+            if (moved)
+                again = true;
+            else {
+                int add = 0;
+                const double al1 = al;
+                for (int k = tid; k < ni; k += T) {
+                    if (ixx[k] || !ju[k]) continue;
+                    const double ga = fabs(g[k]);
+                    Gga[k] = ga;
+                    if (ga > al1 * vq[k]) {
+                        ixx[k] = 1;
+                        add = 1;
+                    }
+                }
+                if (__syncthreads_or(add)) again = true;
+            }
+        }
+        if (!again) {
+            // ---- lambda ilm is done: record it on the caller's scale ----
+            double part = 0.0;
+            int nz = 0;
+            for (int j = tid; j < ni; j += T) {
+                const double bj = (b[j] != 0.0) ? b[j] / Gxs[j] : 0.0;
+                f.beta[(size_t)ilm * ni + j] = bj;
+                part += bj * Gxm[j];
+                nz += (b[j] != 0.0);
+            }
+            const double dotbm = bsum_all(part, red);
+            const int me = (int)bsum_all((double)nz, red);
+            const double devr = (dev1 - devsum) / dev0;
+            const double dprev = ilm > 0 ? f.dev[ilm - 1] : 0.0;
+            if (tid == 0) {
+                f.a0[ilm] = b0 - dotbm;
+                f.alm[ilm] = al;
+                f.dev[ilm] = devr;
+                si[SI_LMU] = ilm + 1;
+            }
+            bool stop = stop_path;
+            if (!stop && ilm + 1 >= mnl && f.flmin < 1.0) {
+                if (me > ni + 1) stop = true;
+                if (devr > GLM_DEVMAX) stop = true;
+                if (devr - dprev < GLM_FDEV) stop = true;  // [EXT] absolute, as in glmnet 2.0-x
+            }
+            ++ilm;
+            if (stop || ilm >= nlam)
+                finished = true;
+            else
+                begin_lambda = true;
+        }
+    }
+    if (begin_lambda) {
+        al0 = al;
+        if (f.flmin >= 1.0)
+            al = f.ulam[ilm];
+        else if (ilm > 1)
+            al *= alf;
+        else if (ilm == 0)
+            al = GLM_BIG;
+        else {
+            double t = 0.0;
+            for (int j = tid; j < ni; j += T)
+                if (ju[j] && vq[j] > 0.0) t = fmax(t, Gga[j] / vq[j]);
+            al0 = bmax_all(t, red);
+            al = alf * al0;
+        }
+        const double tlam = 2.0 * al - al0;
+        for (int k = tid; k < ni; k += T)
+            if (!ixx[k] && ju[k] && Gga[k] > tlam * vq[k]) ixx[k] = 1;
+        __syncthreads();
+    }
+    if (!finished) {
+        // ---- solve the penalised quadratic for the current lambda (lognet2n inner loops) ----
+        const double al1 = al;
+        if (tid == 0) sd[SD_BS0] = b0;
+        for (int j = tid; j < ni; j += T) {
+            Gbs[j] = b[j];
+            xv[j] = H[(size_t)j * ni + j];
+            Gxv[j] = xv[j];
+        }
+        __syncthreads();
+        bool fail = false;
+        for (;;) {
+            ++nlp;
+            double dlx = 0.0;
+            for (int k = 0; k < ni; ++k) {
+                if (!ixx[k]) continue;
+                const double bk = b[k], gk = g[k], xk = xv[k];
+                const double u = gk + xk * bk, au = fabs(u) - vq[k] * al1;
+                const double bn = au <= 0.0 ? 0.0 : copysign(au, u) / xk;
+                const double d = bn - bk;
+                if (fabs(d) <= 0.0) continue;
+                dlx = fmax(dlx, xk * d * d);
+                const bool fresh = (mm[k] == 0);
+                if (fresh) ++nin;
+                sr -= d * hxs[k];
+                __syncthreads();
+                if (tid == 0) {
+                    b[k] = bn;
+                    if (fresh) {
+                        mm[k] = nin;
+                        ml[nin - 1] = k;
+                    }
+                }
+                const double *hk = H + (size_t)k * ni;
+                for (int j = tid; j < ni; j += T) g[j] -= d * hk[j];
+                __syncthreads();
+            }
+            {
+                const double d = sr / xmz;
+                if (d != 0.0) {
+                    b0 += d;
+                    dlx = fmax(dlx, xmz * d * d);
+                    __syncthreads();
+                    for (int j = tid; j < ni; j += T) g[j] -= d * hxs[j];
+                    sr -= d * xmz;
+                    __syncthreads();
+                }
+            }
+            if (dlx < shr) break;
+            if (nlp > f.maxit) {
+                fail = true;
+                break;
+            }
+            for (;;) {
+                ++nlp;
+                dlx = 0.0;
+                for (int l = 0; l < nin; ++l) {
+                    const int k = ml[l];
+                    const double bk = b[k], gk = g[k], xk = xv[k];
+                    const double u = gk + xk * bk, au = fabs(u) - vq[k] * al1;
+                    const double bn = au <= 0.0 ? 0.0 : copysign(au, u) / xk;
+                    const double d = bn - bk;
+                    if (fabs(d) <= 0.0) continue;
+                    dlx = fmax(dlx, xk * d * d);
+                    sr -= d * hxs[k];
+                    __syncthreads();
+                    if (tid == 0) b[k] = bn;
+                    const double *hk = H + (size_t)k * ni;
+                    for (int j = tid; j < ni; j += T) g[j] -= d * hk[j];
+                    __syncthreads();
+                }
+                const double d = sr / xmz;
+                if (d != 0.0) {
+                    b0 += d;
+                    dlx = fmax(dlx, xmz * d * d);
+                    __syncthreads();
+                    for (int j = tid; j < ni; j += T) g[j] -= d * hxs[j];
+                    sr -= d * xmz;
+                    __syncthreads();
+                }
+                if (dlx < shr) break;
+                if (nlp > f.maxit) {
+                    fail = true;
+                    break;
+                }
+            }
+            if (fail) break;
+        }
+        if (fail) {
+            jerr = -(ilm + 1);
+            finished = true;
+        }
+        // ---- coefficients for the next evaluation pass, on the raw x scale ----
+        double part = 0.0;
+        for (int j = tid; j < ni; j += T) {
+            const double bj = (b[j] != 0.0) ? b[j] / Gxs[j] : 0.0;
+            f.coef[j] = bj;
+            part += bj * Gxm[j];
+        }
+        const double dotbm = bsum_all(part, red);
+        if (tid == 0) f.coef[ni] = b0 - dotbm;
+    }
+    // ---- state back to global ----
+    for (int j = tid; j < ni; j += T) {
+        Gb[j] = b[j];
+        Gixx[j] = ixx[j];
+        Gmm[j] = mm[j];
+        Gml[j] = ml[j];
+    }
+    if (tid == 0) {
+        sd[SD_B0] = b0;
+        sd[SD_AL] = al;
+        sd[SD_AL0] = al0;
+        sd[SD_DEV0] = dev0;
+        sd[SD_DEV1] = dev1;
+        sd[SD_SHR] = shr;
+        sd[SD_ALF] = alf;
+        si[SI_NIN] = nin;
+        si[SI_ILM] = ilm;
+        si[SI_NLP] = nlp;
+        si[SI_PHASE] = PH_REFRESH;
+        si[SI_ROUNDS] += 1;
+        if (jerr) si[SI_JERR] = jerr;
+        if (finished) {
+            si[SI_DONE] = 1;
+            // fix.lam: lambda[1] was `big`; R rewrites it by log-linear extrapolation before the
+            // sequence is handed to the CV folds
+            if (f.flmin < 1.0 && si[SI_LMU] > 2) f.alm[0] = exp(2.0 * log(f.alm[1]) - log(f.alm[2]));
+        }
+        done_flags[blockIdx.x] = finished ? 1 : 0;
+    }
+}
+
+// ---- held-out binomial deviance of a CV fit at every lambda ---------------------------------
+// rows = the fit's hole (its held-out inner fold).  grid.y = chunks of LC lambdas.
+template <int ITER>
+__global__ void __launch_bounds__(256)
+lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, const double *__restrict__ X,
+                    long long ld, int LC, double *__restrict__ partials /*[gridDim.x][nlam]*/) {
+    const LognetFit f = fits[fid];
+    extern __shared__ double sm[];  // beta chunk [LC][ni] + a0[LC] + red [warps][LC]
+    const int ni = f.ni;
+    const int lmu = f.st_i[4 * (size_t)ni + SI_LMU];
+    const int m0 = blockIdx.y * LC;
+    const int mc = max(0, min(LC, lmu - m0));
+    double *sb = sm, *sa0 = sb + (size_t)LC * ni, *sred = sa0 + LC;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int e = threadIdx.x; e < mc * ni; e += blockDim.x) sb[e] = f.beta[(size_t)m0 * ni + e];
+    for (int e = threadIdx.x; e < mc; e += blockDim.x) sa0[e] = f.a0[m0 + e];
+    __syncthreads();
+    double acc0 = 0.0, acc1 = 0.0;  // lane l accumulates lambdas l and l + 32 of the chunk
+    const long long wstride = (long long)gridDim.x * nw;
+    for (long long t = (long long)blockIdx.x * nw + wid; t < f.hole_len; t += wstride) {
+        const long long pp = f.hole_begin + t;
+        const long long row = f.list ? (long long)__ldg(f.list + pp) : pp;
+        const double *xr = X + (size_t)row * (size_t)ld;
+        double x[2 * ITER];
+#pragma unroll
+        for (int i = 0; i < ITER; ++i) {
+            const int c = 2 * lane + 64 * i;
+            double2 t2 = make_double2(0.0, 0.0);
+            if (c + 1 < ld) t2 = __ldg(reinterpret_cast<const double2 *>(xr + c));
+            x[2 * i] = c < ni ? t2.x : 0.0;
+            x[2 * i + 1] = c + 1 < ni ? t2.y : 0.0;
+        }
+        const double yi = __ldg(xr + f.iy);
+        for (int m = 0; m < mc; ++m) {
+            const double *bm = sb + (size_t)m * ni;
+            double dot = 0.0;
+#pragma unroll
+            for (int i = 0; i < ITER; ++i) {
+                const int c = 2 * lane + 64 * i;
+                if (c < ni) dot += x[2 * i] * bm[c];
+                if (c + 1 < ni) dot += x[2 * i + 1] * bm[c + 1];
+            }
+            const double eta = sa0[m] + warp_sum(dot);
+            if ((m & 31) == lane) {
+                double pr = 1.0 / (1.0 + exp(-eta));
+                pr = fmin(fmax(pr, 1.0e-5), 1.0 - 1.0e-5);
+                const double dv = -2.0 * (yi * log(pr) + (1.0 - yi) * log(1.0 - pr));
+                if (m < 32)
+                    acc0 += dv;
+                else
+                    acc1 += dv;
+            }
+        }
+    }
+    if (lane < LC) sred[(size_t)wid * LC + lane] = acc0;
+    if (lane + 32 < LC) sred[(size_t)wid * LC + lane + 32] = acc1;
+    __syncthreads();
+    for (int m = threadIdx.x; m < mc; m += blockDim.x) {
+        double s = 0.0;
+        for (int q = 0; q < nw; ++q) s += sred[(size_t)q * LC + m];
+        partials[(size_t)blockIdx.x * f.nlam + m0 + m] = s;
+    }
+}
+
+// ---- prediction on a row list ----------------------------------------------------------------
+template <int ITER>
+__global__ void __launch_bounds__(256)
+predict_rows_kernel(const double *__restrict__ X, long long ld, int ni, const int32_t *__restrict__ rows,
+                    long long row_begin, long long nrows, const double *__restrict__ beta, double a0,
+                    double extra, int mode, int scatter, double *__restrict__ out0,
+                    double *__restrict__ out1) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    double b[2 * ITER];
+#pragma unroll
+    for (int i = 0; i < ITER; ++i) {
+        const int c = 2 * lane + 64 * i;
+        b[2 * i] = c < ni ? beta[c] : 0.0;
+        b[2 * i + 1] = c + 1 < ni ? beta[c + 1] : 0.0;
+    }
+    const long long wstride = (long long)gridDim.x * nw;
+    for (long long t = (long long)blockIdx.x * nw + wid; t < nrows; t += wstride) {
+        const long long row = rows ? (long long)__ldg(rows + row_begin + t) : row_begin + t;
+        const double *xr = X + (size_t)row * (size_t)ld;
+        double dot = 0.0;
+#pragma unroll
+        for (int i = 0; i < ITER; ++i) {
+            const int c = 2 * lane + 64 * i;
+            if (c + 1 < ld) {
+                const double2 t2 = __ldg(reinterpret_cast<const double2 *>(xr + c));
+                dot += t2.x * b[2 * i] + t2.y * b[2 * i + 1];
+            }
+        }
+        const double eta = a0 + warp_sum(dot);
+        if (lane == 0) {
+            const long long o = scatter ? row : t;
+            if (mode == 0)
+                out0[o] = eta;
+            else if (mode == 1)
+                out0[o] = 1.0 / (1.0 + exp(-eta));
+            else {
+                out0[o] = eta;
+                out1[o] = eta + extra;
+            }
+        }
+    }
+}
+
+template <typename F>
+int dispatch_iter(int ni, F &&fn) {
+    const int it = (ni + 63) / 64;
+    if (it <= 1) return fn(std::integral_constant<int, 1>());
+    if (it <= 2) return fn(std::integral_constant<int, 2>());
+    if (it <= 4) return fn(std::integral_constant<int, 4>());
+    if (it <= 8) return fn(std::integral_constant<int, 8>());
+    if (it <= 16) return fn(std::integral_constant<int, 16>());
+    return -1;
+}
+
+}  // namespace
+
+int ate_i_predict_rows(ate_ctx *ctx, const double *X, long long ld, int ni, const int32_t *rows,
+                       long long row_begin, long long nrows, const double *d_beta, double a0, double extra,
+                       int mode, int scatter, double *out0, double *out1) {
+    if (nrows <= 0) return 0;
+    int blocks = ctx->num_sms * 4;
+    long long need = (nrows + 7) / 8;
+    if (need < blocks) blocks = (int)need;
+    int rc = dispatch_iter(ni, [&](auto it) {
+        constexpr int IT = decltype(it)::value;
+        predict_rows_kernel<IT><<<blocks, 256, 0, ctx->stream>>>(X, ld, ni, rows, row_begin, nrows, d_beta, a0,
+                                                                 extra, mode, scatter, out0, out1);
+        return 0;
+    });
+    if (rc < 0) return ate_fail(ctx, -1, "predict: ni = %d too large", ni);
+    ATE_LAUNCHED(ctx);
+    return 0;
+}
+
+int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int iy,
+                      const double *vp_host, const PathOpts &po, const std::vector<CvProblem> &probs,
+                      std::vector<CvOut> &outs, int *rounds_out) {
+    const int P = (int)probs.size();
+    if (P == 0) return 0;
+    if (ni > 1024) return ate_fail(ctx, -1, "cv_binomial: ni = %d too large", ni);
+    const int nlam = po.flmin >= 1.0 ? po.nulam : po.nlam;
+    if (nlam < 1) return ate_fail(ctx, -1, "cv_binomial: need at least one lambda");
+    const int F = probs[0].nseg;
+    for (auto &pr : probs)
+        if (pr.nseg != F) return ate_fail(ctx, -1, "cv_binomial: problems must share nfolds");
+    const int nlead = P, nfol = P * F, nfits = nlead + nfol;
+    const size_t n2 = (size_t)ni * ni;
+
+    // ---- buffers ----
+    size_t vr_total = 0;
+    std::vector<size_t> vr_off(nfits);
+    std::vector<long long> fit_nt(nfits), fit_hb(nfits), fit_hl(nfits);
+    for (int p = 0; p < P; ++p) {
+        fit_nt[p] = probs[p].nt; fit_hb[p] = probs[p].nt; fit_hl[p] = 0;
+        for (int f = 0; f < F; ++f) {
+            const int id = nlead + p * F + f;
+            fit_hb[id] = probs[p].seg[f];
+            fit_hl[id] = probs[p].seg[f + 1] - probs[p].seg[f];
+            fit_nt[id] = probs[p].nt - fit_hl[id];
+        }
+    }
+    for (int id = 0; id < nfits; ++id) {
+        vr_off[id] = vr_total;
+        vr_total += 2 * (size_t)fit_nt[id];
+    }
+    const int plen = 2 * ni + SU_N;
+    const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 4 * (size_t)ni + SI_N;
+    const size_t out_len = 3 * (size_t)nlam + (size_t)ni * nlam;
+    DevBuf<double> dvr, dH, dsums, dcoef, dstd, dout, dvp, dulam, dpart;
+    DevBuf<int> dsti, ddone, dnl;
+    DevBuf<LognetFit> dfits;
+    ATE_CUDA(ctx, dvr.alloc(vr_total));
+    ATE_CUDA(ctx, dH.alloc(n2 * nfits));
+    ATE_CUDA(ctx, dsums.alloc((size_t)plen * nfits));
+    ATE_CUDA(ctx, dcoef.alloc((size_t)(ni + 1) * nfits));
+    ATE_CUDA(ctx, dstd.alloc(sd_len * nfits));
+    ATE_CUDA(ctx, dsti.alloc(si_len * nfits));
+    ATE_CUDA(ctx, dout.alloc(out_len * nfits));
+    ATE_CUDA(ctx, ddone.alloc(nfits));
+    ATE_CUDA(ctx, dfits.alloc(nfits));
+    ATE_CUDA(ctx, cudaMemsetAsync(dout.p, 0, sizeof(double) * out_len * nfits, ctx->stream));
+    ATE_CUDA(ctx, cudaMemsetAsync(ddone.p, 0, sizeof(int) * nfits, ctx->stream));
+    const int ev_blocks = ctx->num_sms * 2;
+    ATE_CUDA(ctx, dpart.alloc((size_t)ev_blocks * (plen > nlam ? plen : nlam)));
+    if (vp_host) {
+        ATE_CUDA(ctx, dvp.alloc(ni));
+        ATE_CUDA(ctx, cudaMemcpyAsync(dvp.p, vp_host, sizeof(double) * ni, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (po.flmin >= 1.0) {
+        ATE_CUDA(ctx, dulam.alloc(nlam));
+        ATE_CUDA(ctx, cudaMemcpyAsync(dulam.p, po.ulam, sizeof(double) * nlam, cudaMemcpyHostToDevice, ctx->stream));
+        ATE_CUDA(ctx, dnl.alloc(1));
+        ATE_CUDA(ctx, cudaMemcpyAsync(dnl.p, &nlam, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    std::vector<LognetFit> hf(nfits);
+    for (int id = 0; id < nfits; ++id) {
+        const int p = id < nlead ? id : (id - nlead) / F;
+        LognetFit &g = hf[id];
+        g.list = probs[p].d_list;
+        g.nt = fit_nt[id]; g.hole_begin = fit_hb[id]; g.hole_len = fit_hl[id];
+        g.ni = ni; g.iy = iy;
+        g.vp = vp_host ? dvp.p : nullptr;
+        g.nlam = nlam; g.thr = po.thr; g.maxit = po.maxit;
+        g.v = dvr.p + vr_off[id];
+        g.r = g.v + fit_nt[id];
+        g.H = dH.p + n2 * id;
+        g.sums = dsums.p + (size_t)plen * id;
+        g.coef = dcoef.p + (size_t)(ni + 1) * id;
+        g.st_d = dstd.p + sd_len * id;
+        g.st_i = dsti.p + si_len * id;
+        double *o = dout.p + out_len * id;
+        g.alm = o; g.a0 = o + nlam; g.dev = o + 2 * nlam; g.beta = o + 3 * nlam;
+        if (id < nlead) {
+            g.flmin = po.flmin;
+            g.ulam = po.flmin >= 1.0 ? dulam.p : nullptr;
+            g.nlam_ptr = po.flmin >= 1.0 ? dnl.p : nullptr;
+        } else {
+            g.flmin = 1.0;
+            g.ulam = hf[p].alm;
+            g.nlam_ptr = hf[p].st_i + 4 * (size_t)ni + SI_LMU;
+        }
+    }
+    ATE_CUDA(ctx, cudaMemcpyAsync(dfits.p, hf.data(), sizeof(LognetFit) * nfits, cudaMemcpyHostToDevice, ctx->stream));
+
+    const size_t ev_smem = sizeof(double) * (size_t)(EV_THREADS / 32) * plen;
+    const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * 4 * (size_t)ni;
+    if (ev_smem > 200 * 1024 || cd_smem > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
+    int rc = dispatch_iter(ni, [&](auto it) {
+        constexpr int IT = decltype(it)::value;
+        if (ev_smem > 48 * 1024)
+            if (cudaFuncSetAttribute(lognet_eval_kernel<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ev_smem) != cudaSuccess) return -1;
+        return 0;
+    });
+    if (rc < 0) return ate_fail(ctx, -1, "cv_binomial: cannot size eval kernel");
+    if (cd_smem > 48 * 1024)
+        ATE_CUDA(ctx, cudaFuncSetAttribute(lognet_cd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cd_smem));
+
+    lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits.p, X, ld);
+    ATE_LAUNCHED(ctx);
+
+    std::vector<int> hdone(nfits, 0);
+    int rounds = 0;
+    const int max_rounds = nlam * 60 + 100;
+    // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds
+    for (int phase = 0; phase < 2; ++phase) {
+        const int lo = phase == 0 ? 0 : nlead, hi = phase == 0 ? nlead : nfits;
+        if (lo == hi) continue;
+        for (;;) {
+            int live = 0;
+            for (int id = lo; id < hi; ++id) {
+                if (hdone[id]) continue;
+                ++live;
+                int rc2 = dispatch_iter(ni, [&](auto it) {
+                    constexpr int IT = decltype(it)::value;
+                    lognet_eval_kernel<IT><<<ev_blocks, EV_THREADS, ev_smem, ctx->stream>>>(dfits.p, id, X, ld, dpart.p);
+                    return 0;
+                });
+                (void)rc2;
+                ATE_LAUNCHED(ctx);
+                fold_partials_kernel<<<(plen + 255) / 256, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, plen, hf[id].sums);
+                ATE_LAUNCHED(ctx);
+                ATE_TRY(ate_i_gram(ctx, X, ld, ni, hf[id].list, 0, hf[id].nt, hf[id].v, hf[id].H,
+                                   hf[id].hole_begin, hf[id].hole_len));
+            }
+            if (!live) break;
+            lognet_cd_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits.p + lo, ddone.p + lo);
+            ATE_LAUNCHED(ctx);
+            ATE_CUDA(ctx, cudaMemcpyAsync(hdone.data() + lo, ddone.p + lo, sizeof(int) * (hi - lo), cudaMemcpyDeviceToHost, ctx->stream));
+            ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
+        }
+    }
+    if (rounds_out) *rounds_out = rounds;
+
+    // ---- held-out deviance of every CV fold at every lambda ----
+    std::vector<double> hcv;
+    if (F > 0) {
+        int LC = (int)((96 * 1024) / (sizeof(double) * (size_t)ni));
+        if (LC > 64) LC = 64;
+        if (LC < 1) LC = 1;
+        const int nchunk = (nlam + LC - 1) / LC;
+        const size_t cv_smem = sizeof(double) * ((size_t)LC * ni + LC + 8 * (size_t)LC);
+        rc = dispatch_iter(ni, [&](auto it) {
+            constexpr int IT = decltype(it)::value;
+            if (cudaFuncSetAttribute(lognet_cvdev_kernel<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cv_smem) != cudaSuccess) return -1;
+            return 0;
+        });
+        if (rc < 0) return ate_fail(ctx, -1, "cv_binomial: cannot size cv kernel");
+        DevBuf<double> dcv;
+        ATE_CUDA(ctx, dcv.alloc((size_t)nfol * nlam));
+        ATE_CUDA(ctx, cudaMemsetAsync(dcv.p, 0, sizeof(double) * (size_t)nfol * nlam, ctx->stream));
+        for (int q = 0; q < nfol; ++q) {
+            const int id = nlead + q;
+            ATE_CUDA(ctx, cudaMemsetAsync(dpart.p, 0, sizeof(double) * (size_t)ev_blocks * nlam, ctx->stream));
+            dispatch_iter(ni, [&](auto it) {
+                constexpr int IT = decltype(it)::value;
+                lognet_cvdev_kernel<IT><<<dim3(ev_blocks, nchunk), 256, cv_smem, ctx->stream>>>(dfits.p, id, X, ld, LC, dpart.p);
+                return 0;
+            });
+            ATE_LAUNCHED(ctx);
+            fold_partials_kernel<<<(nlam + 255) / 256, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, nlam, dcv.p + (size_t)q * nlam);
+            ATE_LAUNCHED(ctx);
+        }
+        hcv.resize((size_t)nfol * nlam);
+        ATE_CUDA(ctx, cudaMemcpyAsync(hcv.data(), dcv.p, sizeof(double) * hcv.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    std::vector<double> hout(out_len * (size_t)nlead), hsd(sd_len * (size_t)nfits);
+    std::vector<int> hsi(si_len * (size_t)nfits);
+    ATE_CUDA(ctx, cudaMemcpyAsync(hout.data(), dout.p, sizeof(double) * hout.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    ATE_CUDA(ctx, cudaMemcpyAsync(hsd.data(), dstd.p, sizeof(double) * hsd.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    ATE_CUDA(ctx, cudaMemcpyAsync(hsi.data(), dsti.p, sizeof(int) * hsi.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+
+    outs.assign(P, CvOut());
+    for (int p = 0; p < P; ++p) {
+        CvOut &o = outs[p];
+        const int *iv = hsi.data() + si_len * (size_t)p + 4 * (size_t)ni;
+        const double *dv = hsd.data() + sd_len * (size_t)p + 7 * (size_t)ni;
+        o.lmu = iv[SI_LMU];
+        o.nlp = iv[SI_NLP];
+        o.jerr = iv[SI_JERR];
+        const double *ob = hout.data() + out_len * (size_t)p;
+        o.lambda.assign(ob, ob + o.lmu);
+        o.a0.assign(ob + nlam, ob + nlam + o.lmu);
+        o.dev.assign(ob + 2 * nlam, ob + 2 * nlam + o.lmu);
+        o.beta.assign(ob + 3 * nlam, ob + 3 * nlam + (size_t)ni * o.lmu);
+        o.nulldev = 2.0 * (double)probs[p].nt * dv[SD_DEV0];
+        if (F > 0 && o.lmu > 0) {
+            std::vector<double> cvk((size_t)F * o.lmu), wk(F);
+            std::vector<int> nlk(F);
+            for (int f = 0; f < F; ++f) {
+                const int id = nlead + p * F + f;
+                const int *fv = hsi.data() + si_len * (size_t)id + 4 * (size_t)ni;
+                nlk[f] = fv[SI_LMU] < o.lmu ? fv[SI_LMU] : o.lmu;
+                if (fv[SI_JERR] != 0 && o.jerr == 0) o.jerr = fv[SI_JERR];
+                o.nlp += fv[SI_NLP];
+                wk[f] = (double)fit_hl[id];
+                for (int l = 0; l < o.lmu; ++l)
+                    cvk[(size_t)f * o.lmu + l] = hcv[((size_t)p * F + f) * nlam + l] / wk[f];
+            }
+            ate_host_cv_summary(cvk, wk, nlk, F, o.lmu, o.lambda.data(), o.cvm, o.cvsd, &o.idx_min, &o.idx_1se);
+        }
+    }
+    return 0;
+}
