@@ -30,6 +30,7 @@ class CrossfitOpts(C.Structure):
         ("boot_seed", C.c_uint64), ("boot_rep_offset", c_ll), ("boot_reps_here", C.c_int),
         ("r_seed", C.c_uint32), ("rng_kind", C.c_int), ("on_device", C.c_int),
         ("fold_begin", C.c_int), ("fold_end", C.c_int), ("skip_score", C.c_int),
+        ("shard_rank", C.c_int), ("shard_count", C.c_int),
     ]
 
 
@@ -39,9 +40,12 @@ class CrossfitResult(C.Structure):
         ("lower_ci", C.c_double), ("upper_ci", C.c_double), ("jerr", C.c_int),
         ("rounds_irls", C.c_int), ("gram_launches", c_ll), ("ms_design", C.c_double),
         ("ms_outcome", C.c_double), ("ms_propensity", C.c_double), ("ms_score", C.c_double),
-        ("ms_bootstrap", C.c_double),
+        ("ms_bootstrap", C.c_double), ("irls_solves", C.c_double), ("strong_mean", C.c_double),
+        ("strong_frac2", C.c_double),
     ]
 
+
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_double), C.c_longlong)
 
 # every symbol include/ate_b200.h declares: name -> (restype, argtypes)
 _vp = C.c_void_p
@@ -50,6 +54,8 @@ SIGNATURES = {
     "ate_ctx_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
     "ate_ctx_destroy": (None, [_vp]),
     "ate_last_error": (C.c_char_p, [_vp]),
+    "ate_ctx_stream": (_vp, [_vp]),
+    "ate_ctx_set_allreduce": (C.c_int, [_vp, _vp, _vp]),
     "ate_launch_count": (c_ll, [_vp]),
     "ate_profile_enable": (C.c_int, [_vp, C.c_int]),
     "ate_profile_read": (C.c_int, [_vp, c_dp, C.POINTER(c_ll), c_dp, c_dp]),

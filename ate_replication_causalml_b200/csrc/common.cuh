@@ -35,6 +35,9 @@ struct ate_ctx {
     void *gram_scratch = nullptr;
     size_t gram_scratch_bytes = 0;
     ate_rng_state rng;
+    // multi-GPU: host-buffer sum over the ranks that share one fit
+    ate_allreduce_fn allreduce = nullptr;
+    void *allreduce_user = nullptr;
 };
 
 // ---- error handling ------------------------------------------------------------------

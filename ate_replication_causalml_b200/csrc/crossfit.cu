@@ -1,6 +1,7 @@
 // crossfit.cu -- public glmnet / cv.glmnet / predict entry points and the K-fold cross-fitted
 // AIPW composite (steps 1-6 of the coverage contract).
 #include <math.h>
+#include <string.h>
 
 #include <chrono>
 
@@ -210,6 +211,8 @@ extern "C" void ate_crossfit_default_opts(ate_crossfit_opts *o) {
     o->fold_begin = 0;
     o->fold_end = 0;
     o->skip_score = 0;
+    o->shard_rank = 0;
+    o->shard_count = 0;
 }
 
 extern "C" int ate_crossfit_aipw(ate_ctx *ctx, const ate_crossfit_opts *opts, long long n, int p0,
@@ -334,6 +337,11 @@ extern "C" int ate_crossfit_aipw(ate_ctx *ctx, const ate_crossfit_opts *opts, lo
     po.thr = o.thresh > 0 ? o.thresh : 1e-7;
     po.maxit = o.maxit > 0 ? o.maxit : 100000;
     po.flmin = 1.0e-4;  // nobs >= nvars on every training set we accept
+    if (o.shard_count > 1) {
+        if (o.shard_rank < 0 || o.shard_rank >= o.shard_count) return ate_fail(ctx, -1, "ate_crossfit_aipw: bad shard rank");
+        po.shard_rank = o.shard_rank;
+        po.shard_count = o.shard_count;
+    }
     DevBuf<double> dbeta;
     ATE_CUDA(ctx, dbeta.alloc((size_t)p + 1));
     int worst = 0;
@@ -364,9 +372,14 @@ extern "C" int ate_crossfit_aipw(ate_ctx *ctx, const ate_crossfit_opts *opts, lo
     //          type = "response" at the selected lambda (:144) ----
     {
         std::vector<CvOut> outs;
-        int rounds = 0;
-        ATE_TRY(ate_i_cv_binomial(ctx, dX.p, ld, p, p, nullptr, po, prob_ps, outs, &rounds));
-        res->rounds_irls = rounds;
+        IrlsStats st;
+        ATE_TRY(ate_i_cv_binomial(ctx, dX.p, ld, p, p, nullptr, po, prob_ps, outs, &st));
+        res->rounds_irls = st.rounds;
+        res->irls_solves = st.solves;
+        if (st.solves > 0) {
+            res->strong_mean = st.sum_strong / st.solves;
+            res->strong_frac2 = st.sum_strong2 / st.solves / ((double)p * p);
+        }
         for (int q = 0; q < nk; ++q) {
             const CvOut &c = outs[q];
             if (c.jerr > 0 || c.lmu < 1) return ate_fail(ctx, -3, "propensity fit of fold %d failed (jerr %d)", kb + q, c.jerr);

@@ -63,6 +63,15 @@ extern "C" const char *ate_last_error(const ate_ctx *ctx) {
     return ctx ? ctx->err.c_str() : g_create_err.c_str();
 }
 
+extern "C" void *ate_ctx_stream(const ate_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+extern "C" int ate_ctx_set_allreduce(ate_ctx *ctx, ate_allreduce_fn fn, void *user) {
+    if (!ctx) return -1;
+    ctx->allreduce = fn;
+    ctx->allreduce_user = user;
+    return 0;
+}
+
 extern "C" long long ate_launch_count(const ate_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
 extern "C" int ate_profile_enable(ate_ctx *ctx, int on) {

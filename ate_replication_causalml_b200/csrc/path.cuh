@@ -37,15 +37,20 @@ struct PathOpts {
     int nulam = 0;
     double thr = 1.0e-7;
     int maxit = 100000;
+    int shard_rank = 0, shard_count = 1;  // cv-fold paths dealt round-robin over ranks
 };
 
 // X: row-major design, features are columns [0, ni); iy / i1: response and ones columns.
 int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int iy, int i1,
                       const double *vp_host, const PathOpts &po, const std::vector<CvProblem> &probs,
                       std::vector<CvOut> &outs);
+struct IrlsStats {
+    int rounds = 0;
+    double solves = 0.0, sum_strong = 0.0, sum_strong2 = 0.0;
+};
 int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int iy,
                       const double *vp_host, const PathOpts &po, const std::vector<CvProblem> &probs,
-                      std::vector<CvOut> &outs, int *rounds_out);
+                      std::vector<CvOut> &outs, IrlsStats *stats);
 
 // cvm / cvsd / getmin from per-fold means (host).  cvk[f*lmu + l], wk[f] fold sizes, nlk[f] number
 // of lambdas fold f returned.

@@ -25,7 +25,7 @@
 namespace {
 
 enum { PH_INIT = 0, PH_REFRESH = 1 };
-enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_N };
+enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_SUMS, SD_SUMS2, SD_SUMA, SD_N };
 enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_N };
 // sums layout: gr[ni], hx[ni], then XMZ, SR, DEV
 enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
@@ -33,7 +33,7 @@ enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
 struct LognetFit {
     const int32_t *list;  // row ids (NULL = identity)
     long long nt, hole_begin, hole_len;
-    int ni, iy;
+    int ni, iy, owned;
     const double *vp;
     double flmin;
     const double *ulam;
@@ -179,6 +179,7 @@ lognet_init_kernel(const LognetFit *__restrict__ fits, const double *__restrict_
         sd[SD_BZ] = bz;
         sd[SD_B0] = bz;
         si[SI_PHASE] = PH_INIT;
+        if (!f.owned) si[SI_DONE] = 1;  // another rank solves this cv-fold path
         if (q0 <= GLM_PMIN) {
             si[SI_JERR] = 8001;
             si[SI_DONE] = 1;
@@ -388,6 +389,16 @@ lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flag
     if (!finished) {
         // ---- solve the penalised quadratic for the current lambda (lognet2n inner loops) ----
         const double al1 = al;
+        {   // statistics: size of the strong set this round (what a column-restricted Gram would need)
+            int cs = 0;
+            for (int j = tid; j < ni; j += T) cs += ixx[j];
+            const double ns = bsum_all((double)cs, red);
+            if (tid == 0) {
+                sd[SD_SUMS] += ns;
+                sd[SD_SUMS2] += ns * ns;
+                sd[SD_SUMA] += (double)nin;
+            }
+        }
         if (tid == 0) sd[SD_BS0] = b0;
         for (int j = tid; j < ni; j += T) {
             Gbs[j] = b[j];
@@ -658,7 +669,7 @@ int ate_i_predict_rows(ate_ctx *ctx, const double *X, long long ld, int ni, cons
 
 int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int iy,
                       const double *vp_host, const PathOpts &po, const std::vector<CvProblem> &probs,
-                      std::vector<CvOut> &outs, int *rounds_out) {
+                      std::vector<CvOut> &outs, IrlsStats *stats) {
     const int P = (int)probs.size();
     if (P == 0) return 0;
     if (ni > 1024) return ate_fail(ctx, -1, "cv_binomial: ni = %d too large", ni);
@@ -723,6 +734,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         g.list = probs[p].d_list;
         g.nt = fit_nt[id]; g.hole_begin = fit_hb[id]; g.hole_len = fit_hl[id];
         g.ni = ni; g.iy = iy;
+        g.owned = (id < nlead || po.shard_count <= 1 || ((id - nlead) % po.shard_count) == po.shard_rank) ? 1 : 0;
         g.vp = vp_host ? dvp.p : nullptr;
         g.nlam = nlam; g.thr = po.thr; g.maxit = po.maxit;
         g.v = dvr.p + vr_off[id];
@@ -763,6 +775,8 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     ATE_LAUNCHED(ctx);
 
     std::vector<int> hdone(nfits, 0);
+    for (int id = 0; id < nfits; ++id)
+        if (!hf[id].owned) hdone[id] = 1;
     int rounds = 0;
     const int max_rounds = nlam * 60 + 100;
     // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds
@@ -794,7 +808,6 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
         }
     }
-    if (rounds_out) *rounds_out = rounds;
 
     // ---- held-out deviance of every CV fold at every lambda ----
     std::vector<double> hcv;
@@ -815,6 +828,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         ATE_CUDA(ctx, cudaMemsetAsync(dcv.p, 0, sizeof(double) * (size_t)nfol * nlam, ctx->stream));
         for (int q = 0; q < nfol; ++q) {
             const int id = nlead + q;
+            if (!hf[id].owned) continue;
             ATE_CUDA(ctx, cudaMemsetAsync(dpart.p, 0, sizeof(double) * (size_t)ev_blocks * nlam, ctx->stream));
             dispatch_iter(ni, [&](auto it) {
                 constexpr int IT = decltype(it)::value;
@@ -835,6 +849,37 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     ATE_CUDA(ctx, cudaMemcpyAsync(hsi.data(), dsti.p, sizeof(int) * hsi.size(), cudaMemcpyDeviceToHost, ctx->stream));
     ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 
+    if (stats) {
+        stats->rounds = rounds;
+        for (int id = 0; id < nfits; ++id) {
+            if (!hf[id].owned) continue;
+            const double *dv = hsd.data() + sd_len * (size_t)id + 7 * (size_t)ni;
+            const int *iv = hsi.data() + si_len * (size_t)id + 4 * (size_t)ni;
+            stats->solves += iv[SI_ROUNDS];
+            stats->sum_strong += dv[SD_SUMS];
+            stats->sum_strong2 += dv[SD_SUMS2];
+        }
+    }
+    // ---- ranks sharing this fit: every cv-fold path was solved by exactly one of them ----
+    std::vector<double> fstat((size_t)nfol * 3, 0.0);  // lmu, nlp, jerr of each cv-fold path
+    for (int q = 0; q < nfol; ++q) {
+        const int id = nlead + q;
+        if (!hf[id].owned) continue;
+        const int *fv = hsi.data() + si_len * (size_t)id + 4 * (size_t)ni;
+        fstat[3 * q] = fv[SI_LMU];
+        fstat[3 * q + 1] = fv[SI_NLP];
+        fstat[3 * q + 2] = fv[SI_JERR];
+    }
+    if (po.shard_count > 1 && F > 0) {
+        if (!ctx->allreduce) return ate_fail(ctx, -1, "cv_binomial: sharded fit but no all-reduce hook set");
+        for (int q = 0; q < nfol; ++q)
+            if (!hf[nlead + q].owned)
+                for (int l = 0; l < nlam; ++l) hcv[(size_t)q * nlam + l] = 0.0;
+        if (ctx->allreduce(ctx->allreduce_user, hcv.data(), (long long)hcv.size()) != 0 ||
+            ctx->allreduce(ctx->allreduce_user, fstat.data(), (long long)fstat.size()) != 0)
+            return ate_fail(ctx, -4, "cv_binomial: all-reduce hook failed");
+    }
+
     outs.assign(P, CvOut());
     for (int p = 0; p < P; ++p) {
         CvOut &o = outs[p];
@@ -854,10 +899,10 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             std::vector<int> nlk(F);
             for (int f = 0; f < F; ++f) {
                 const int id = nlead + p * F + f;
-                const int *fv = hsi.data() + si_len * (size_t)id + 4 * (size_t)ni;
-                nlk[f] = fv[SI_LMU] < o.lmu ? fv[SI_LMU] : o.lmu;
-                if (fv[SI_JERR] != 0 && o.jerr == 0) o.jerr = fv[SI_JERR];
-                o.nlp += fv[SI_NLP];
+                const double *fv = fstat.data() + 3 * (size_t)(p * F + f);
+                nlk[f] = (int)fv[0] < o.lmu ? (int)fv[0] : o.lmu;
+                if (fv[2] != 0 && o.jerr == 0) o.jerr = (int)fv[2];
+                o.nlp += (int)fv[1];
                 wk[f] = (double)fit_hl[id];
                 for (int l = 0; l < o.lmu; ++l)
                     cvk[(size_t)f * o.lmu + l] = hcv[((size_t)p * F + f) * nlam + l] / wk[f];

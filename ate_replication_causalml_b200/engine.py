@@ -55,6 +55,11 @@ class Engine:
         return rc
 
     @property
+    def stream_ptr(self) -> int:
+        """cudaStream_t of the ctx (wrap with torch.cuda.ExternalStream to record events)."""
+        return int(self._lib.ate_ctx_stream(self._h) or 0)
+
+    @property
     def launches(self) -> int:
         return int(self._lib.ate_launch_count(self._h))
 

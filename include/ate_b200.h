@@ -53,6 +53,9 @@ ATE_API int ate_version(void);
 ATE_API int ate_ctx_create(int device, ate_ctx **out);
 ATE_API void ate_ctx_destroy(ate_ctx *ctx);
 ATE_API const char *ate_last_error(const ate_ctx *ctx);
+/* The ctx's cudaStream_t (as void*), so a caller can record its own CUDA events on the stream
+ * the kernels are launched on. */
+ATE_API void *ate_ctx_stream(const ate_ctx *ctx);
 /* Number of kernels this ctx has launched so far (bench.py's `gpu_launches`). */
 ATE_API long long ate_launch_count(const ate_ctx *ctx);
 /* Device time of the dominant kernel (weighted Gram) accumulated since the last reset, from
@@ -61,6 +64,14 @@ ATE_API long long ate_launch_count(const ate_ctx *ctx);
 ATE_API int ate_profile_enable(ate_ctx *ctx, int on);
 ATE_API int ate_profile_read(ate_ctx *ctx, double *gram_ms, long long *gram_launches, double *gram_flops,
                      double *gram_bytes);
+
+/* Multi-GPU hook (no reference counterpart: the reference is single-threaded).  When one fit is
+ * shared by several ranks (ate_crossfit_opts.shard_count > 1) the library calls `fn` to sum a
+ * small HOST buffer of doubles over all ranks (held-out CV deviances of the cv-fold paths each
+ * rank solved).  The R shim would bind this to ncclAllReduce / MPI_Allreduce; bench.py binds it
+ * to torch.distributed.  Must return 0 on success. */
+typedef int (*ate_allreduce_fn)(void *user, double *host_buf, long long count);
+ATE_API int ate_ctx_set_allreduce(ate_ctx *ctx, ate_allreduce_fn fn, void *user);
 
 /* ---- a1: scale()  (ate_replication.Rmd:72-74) ----------------------------------------- */
 /* In place on x[n*p]: columns `cols` (0-based; NULL = all) get (x-mean)/sd, sd with n-1.
@@ -157,6 +168,8 @@ typedef struct ate_crossfit_opts {
     int fold_begin;     /* outer folds [fold_begin, fold_end) fitted by this call (1-based,   */
     int fold_end;       /*   0,0 = all); rows of other folds get NaN nuisances                */
     int skip_score;     /* 1: stop after the nuisances (multi-GPU drivers combine first)      */
+    int shard_rank;     /* this process's rank and the number of ranks sharing ONE fit: the   */
+    int shard_count;    /*   cv-fold paths are dealt round-robin over ranks (0,0 = no sharding) */
 } ate_crossfit_opts;
 
 ATE_API void ate_crossfit_default_opts(ate_crossfit_opts *o);
@@ -167,6 +180,9 @@ typedef struct ate_crossfit_result {
     int rounds_irls;       /* lock-step IRLS rounds executed                                  */
     long long gram_launches;
     double ms_design, ms_outcome, ms_propensity, ms_score, ms_bootstrap; /* host wall, synced */
+    double irls_solves;     /* total IRLS quadratic solves over all propensity path fits          */
+    double strong_mean;     /* mean size of glmnet's strong set over those solves                 */
+    double strong_frac2;    /* mean of (|strong| / p)^2: the share of Gram flops a solve needs    */
 } ate_crossfit_result;
 
 /* x_base[n*p0] col-major, w[n], y[n].  foldid[n] (1..K) and inner_ps / inner_out [K*n]

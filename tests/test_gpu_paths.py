@@ -1,0 +1,303 @@
+"""GPU parity tests (through the C ABI) of the lambda-path solvers, cv.glmnet, prediction, the
+cross-fitted composite and the host-side mirror of the R entry points.
+
+Tolerances.  On designs without exactly duplicated columns the Gram-space solver follows
+glmnet's iterates to rounding, so coefficients are compared at 1e-9 (the north-star bar is
+"within glmnet's convergence threshold", i.e. ~sqrt(thresh) = 3e-4) and ATE/SE at 1e-9 relative
+(bar: 1e-6).  belloni()'s ordered pairs (ate_functions.R:290-296) DUPLICATE columns (c1*c2 and
+c2*c1); there the split of weight between twins is decided by rounding noise in glmnet itself,
+so those cases compare fitted values and ATE at the convergence-threshold level, and at 1e-6
+once thresh is tightened so that both sides reach the (unique) optimum of the fitted values."""
+import numpy as np
+import pytest
+
+from ate_replication_causalml_b200 import synth
+from conftest import make_folds
+
+pytestmark = pytest.mark.gpu
+
+
+def _data(n, p0):
+    d = synth.make_dataset(n, p0)
+    return d
+
+
+def _scaled(oracle, d):
+    xs, _, _ = oracle.scale(d["x_raw"], cols=np.arange(d["n_continuous"]))
+    return xs
+
+
+def _cmp_path(g, o, tol=1e-9):
+    assert g["jerr"] == o["jerr"] == 0
+    assert g["lmu"] == o["lmu"]
+    assert g["npasses"] == o["npasses"]                      # same iterates, pass for pass
+    assert np.allclose(g["lambda_"], o["lambda_"], rtol=1e-12)
+    assert np.abs(g["beta"] - o["beta"]).max() < tol
+    assert np.abs(g["a0"] - o["a0"]).max() < tol
+    assert np.abs(g["dev_ratio"] - o["dev_ratio"]).max() < tol
+    assert abs(g["nulldev"] - o["nulldev"]) <= 1e-10 * abs(o["nulldev"])
+
+
+@pytest.mark.parametrize("n,p0", [(200, 5), (2000, 5), (5000, 21), (20_000, 40)])
+def test_gaussian_path_with_unpenalised_treatment(engine, oracle, n, p0):
+    d = _data(n, p0)
+    xw = np.column_stack([_scaled(oracle, d), d["w"]])
+    vp = np.r_[np.ones(p0), 0.0]                              # ate_functions.R:98
+    _cmp_path(engine.glmnet(xw, d["y"], "gaussian", penalty_factor=vp),
+              oracle.glmnet(xw, d["y"], "gaussian", penalty_factor=vp))
+
+
+@pytest.mark.parametrize("n,p0", [(200, 5), (2000, 5), (5000, 21), (20_000, 40)])
+def test_binomial_path(engine, oracle, n, p0):
+    d = _data(n, p0)
+    xs = _scaled(oracle, d)
+    _cmp_path(engine.glmnet(xs, d["w"], "binomial"), oracle.glmnet(xs, d["w"], "binomial"))
+
+
+def test_paths_against_golden_fixtures(engine, golden, oracle):
+    reg = golden["reg"]
+    for tag, (n, p0) in {"a": (200, 5), "b": (5000, 21)}.items():
+        d = _data(n, p0)
+        xs = _scaled(oracle, d)
+        g = engine.glmnet(np.column_stack([xs, d["w"]]), d["y"], "gaussian", penalty_factor=np.r_[np.ones(p0), 0.0])
+        assert np.abs(g["beta"] - reg[f"{tag}_g_beta"]).max() < 1e-9 and g["npasses"] == int(reg[f"{tag}_g_npasses"])
+        b = engine.glmnet(xs, d["w"], "binomial")
+        assert np.abs(b["beta"] - reg[f"{tag}_b_beta"]).max() < 1e-9 and b["npasses"] == int(reg[f"{tag}_b_npasses"])
+
+
+def test_paths_against_sklearn_golden(engine, golden):
+    sk = golden["sk"]
+    g = engine.glmnet(sk["X"], sk["y"], "gaussian", thresh=1e-15)
+    assert np.abs(g["beta"][:, 1:] - sk["sk_gauss"]).max() < 1e-8
+    b = engine.glmnet(sk["X"], sk["w"], "binomial", thresh=1e-15)
+    for i, l in enumerate(sk["sel_binom"]):
+        assert np.abs(b["beta"][:, l] - sk["sk_binom"][i][1:]).max() < 1e-7
+
+
+def test_user_lambda_and_lambda_min_ratio(engine, oracle):
+    d = _data(1500, 6)
+    xs = _scaled(oracle, d)
+    lam = np.geomspace(0.2, 0.002, 17)
+    for fam, yy in (("gaussian", d["y"]), ("binomial", d["w"])):
+        _cmp_path(engine.glmnet(xs, yy, fam, lambda_=lam), oracle.glmnet(xs, yy, fam, lambda_=lam))
+        _cmp_path(engine.glmnet(xs, yy, fam, nlambda=30, lambda_min_ratio=0.01),
+                  oracle.glmnet(xs, yy, fam, nlambda=30, lambda_min_ratio=0.01))
+
+
+def test_kkt_holds_at_scale(engine):
+    """n = 200k, p = 64: too slow for the oracle in a test; the optimality conditions are
+    size-independent.  |<x_j, y - p>|/n <= lambda on standardised columns, = for active ones."""
+    n, p0 = 200_000, 8
+    d = _data(n, p0)
+    X = np.column_stack([d["x_raw"][:, [i]] * d["x_raw"][:, i:] for i in range(p0)])  # unique pairs: no twins
+    X = (X - X.mean(0)) / X.std(0)
+    b = engine.glmnet(X, d["w"], "binomial", thresh=1e-12)
+    assert b["jerr"] == 0 and b["lmu"] > 10
+    for l in range(2, b["lmu"], 9):
+        pr = 1 / (1 + np.exp(-(b["a0"][l] + X @ b["beta"][:, l])))
+        g = (X * (d["w"] - pr)[:, None]).mean(0)
+        lam, act = b["lambda_"][l], b["beta"][:, l] != 0
+        assert (np.abs(g[~act]) <= lam * (1 + 1e-5) + 1e-9).all()
+        assert np.abs(np.abs(g[act]) - lam).max() < 1e-6
+        assert abs((d["w"] - pr).mean()) < 1e-8
+
+
+@pytest.mark.parametrize("fam", ["gaussian", "binomial"])
+def test_cv_glmnet_matches_oracle(engine, oracle, fam):
+    d = _data(3000, 9)
+    xs = _scaled(oracle, d)
+    fid = synth.fold_ids(3000, 10, 7)
+    if fam == "gaussian":
+        xx, yy, pf = np.column_stack([xs, d["w"]]), d["y"], np.r_[np.ones(9), 0.0]
+    else:
+        xx, yy, pf = xs, d["w"], None
+    g = engine.cv_glmnet(xx, yy, fam, penalty_factor=pf, foldid=fid)
+    o = oracle.cv_glmnet(xx, yy, fid, fam, penalty_factor=pf)
+    assert g["lmu"] == o["lmu"] and g["idx_min"] == o["idx_min"] and g["idx_1se"] == o["idx_1se"]
+    assert np.allclose(g["cvm"], o["cvm"], rtol=1e-10) and np.allclose(g["cvsd"], o["cvsd"], rtol=1e-8)
+    assert np.abs(g["beta"] - o["beta"]).max() < 1e-9
+
+
+def test_cv_glmnet_draws_r_fold_ids_when_not_given(engine, oracle):
+    d = _data(1200, 5)
+    xs = _scaled(oracle, d)
+    g = engine.cv_glmnet(xs, d["w"], "binomial", nfolds=10, seed=1991, rng_kind=1)
+    oracle.set_seed(1991)
+    fid = oracle.foldid(1200, 10, 1)                          # sample(rep(seq(nfolds), length = N))
+    o = oracle.cv_glmnet(xs, d["w"], fid, "binomial")
+    assert g["idx_1se"] == o["idx_1se"] and np.allclose(g["cvm"], o["cvm"], rtol=1e-10)
+
+
+def test_ragged_and_unequal_folds(engine, oracle):
+    d = _data(997, 4)
+    xs = _scaled(oracle, d)
+    fid = np.r_[np.full(500, 1), np.full(300, 2), np.full(150, 3), np.full(47, 4)].astype(np.int32)
+    np.random.default_rng(1).shuffle(fid)
+    g = engine.cv_glmnet(xs, d["y"], "gaussian", foldid=fid)
+    o = oracle.cv_glmnet(xs, d["y"], fid, "gaussian")
+    assert np.allclose(g["cvm"], o["cvm"], rtol=1e-10) and g["idx_min"] == o["idx_min"]
+
+
+def test_predict_link_and_response(engine, oracle):
+    d = _data(4001, 7)
+    beta = np.r_[0.3, 0, -0.2, 0, 0, 1.5, 0]
+    for resp in (False, True):
+        assert np.abs(engine.predict(d["x_raw"], -0.4, beta, resp) - oracle.predict(d["x_raw"], -0.4, beta, resp)).max() < 1e-13
+
+
+def test_error_paths_report_instead_of_crashing(engine):
+    from ate_replication_causalml_b200._lib import AteError
+    d = _data(300, 4)
+    with pytest.raises(AteError):
+        engine.cv_glmnet(d["x_raw"], d["y"], "gaussian", foldid=np.zeros(300, np.int32))   # ids must be 1-based
+    with pytest.raises(AteError):
+        engine.cv_glmnet(d["x_raw"], d["y"], "gaussian", nfolds=2)
+    with pytest.raises(AteError):
+        engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], K=1)
+    with pytest.raises(AteError):
+        engine.bootstrap(d["w"], d["y"], d["y"], d["y"], d["y"], B=0)
+    with pytest.raises(ValueError):
+        engine.glmnet(d["x_raw"], d["y"][:10])
+    engine.glmnet(d["x_raw"], d["y"])                                                     # ctx still usable
+
+
+# ---------------------------------------------------------------- the composite
+@pytest.mark.parametrize("n,p0", [(2000, 5), (5000, 21)])
+def test_crossfit_matches_oracle_with_supplied_folds_and_indices(engine, oracle, n, p0):
+    d = _data(n, p0)
+    fo, ips, iout = make_folds(n)
+    B = 30
+    oracle.set_seed(7)
+    bidx = np.stack([oracle.sample_replace(n, n, 1) for _ in range(B)])                   # R's sample(), validation mode
+    r = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], foldid=fo, inner_ps=ips, inner_out=iout, boot_idx=bidx,
+                             n_continuous=d["n_continuous"], expand=0, B=B, boot_mode=0)
+    xs = _scaled(oracle, d)
+    o = oracle.crossfit_aipw(xs, d["w"], d["y"], fo, ips, iout)
+    sd, boot = oracle.bootstrap_idx(d["w"], d["y"], o["phat"], o["m0"], o["m1"], bidx)
+    assert np.allclose(r["lambda_ps"], o["lambda_ps"], rtol=1e-10) and np.allclose(r["lambda_out"], o["lambda_out"], rtol=1e-10)
+    assert np.abs(r["phat"] - o["phat"]).max() < 1e-9 and np.abs(r["m0"] - o["m0"]).max() < 1e-9
+    assert abs(r["tau"] - o["tau"]) <= 1e-9 * abs(o["tau"])                                 # bar: 1e-6
+    assert abs(r["se_sandwich"] - o["se"]) <= 1e-9 * o["se"]
+    assert np.abs(r["boot"] - boot).max() < 1e-9 and abs(r["se_bootstrap"] - sd) <= 1e-8 * sd
+    assert abs(r["lower_ci"] - (r["tau"] - 1.96 * r["se_bootstrap"])) < 1e-15
+
+
+def test_crossfit_golden_fixture(engine, golden):
+    reg = golden["reg"]
+    d = _data(5000, 21)
+    fo, ips, iout = make_folds(5000)
+    r = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], foldid=fo, inner_ps=ips, inner_out=iout,
+                             boot_idx=reg["b_boot_idx"], n_continuous=d["n_continuous"], expand=0, B=25, boot_mode=0)
+    assert abs(r["tau"] - float(reg["b_cf_tau"])) <= 1e-9 * abs(float(reg["b_cf_tau"]))
+    assert abs(r["se_sandwich"] - float(reg["b_cf_se"])) <= 1e-9 * float(reg["b_cf_se"])
+    assert np.abs(r["boot"] - reg["b_boot"]).max() < 1e-9
+    assert abs(r["se_bootstrap"] - float(reg["b_boot_sd"])) <= 1e-8 * float(reg["b_boot_sd"])
+
+
+def test_crossfit_draws_all_folds_with_r_rng(engine, oracle):
+    n, p0, K = 1500, 6, 5
+    d = _data(n, p0)
+    r = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], n_continuous=d["n_continuous"], expand=0, B=0, r_seed=42, rng_kind=1)
+    # the same draws in the order R would make them: outer ids, then per k: propensity, outcome
+    oracle.set_seed(42)
+    fo = oracle.foldid(n, K, 1)
+    ips = np.zeros((K, n), np.int32); iout = np.zeros((K, n), np.int32)
+    for k in range(K):
+        nt = int((fo != k + 1).sum())
+        ips[k, :nt] = oracle.foldid(nt, 10, 1)
+        iout[k, :nt] = oracle.foldid(nt, 10, 1)
+    o = oracle.crossfit_aipw(_scaled(oracle, d), d["w"], d["y"], fo, ips, iout)
+    assert abs(r["tau"] - o["tau"]) <= 1e-9 * abs(o["tau"]) and abs(r["se_sandwich"] - o["se"]) <= 1e-9 * o["se"]
+
+
+def test_crossfit_on_belloni_design_with_twin_columns(engine, oracle):
+    n, p0 = 3000, 6
+    d = _data(n, p0)
+    fo, ips, iout = make_folds(n)
+    xd = oracle.expand_deg2(_scaled(oracle, d), True)
+    # default thresh: both sides are converged solutions of the same problem -> threshold-level
+    r = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], foldid=fo, inner_ps=ips, inner_out=iout,
+                             n_continuous=d["n_continuous"], expand=2, B=0)
+    o = oracle.crossfit_aipw(xd, d["w"], d["y"], fo, ips, iout)
+    assert np.allclose(r["lambda_ps"], o["lambda_ps"], rtol=1e-9)        # same lambda chosen
+    assert np.abs(r["phat"] - o["phat"]).max() < 2e-3 and abs(r["tau"] - o["tau"]) <= 1e-4 * abs(o["tau"])
+    # tight thresh: fitted values are unique even if the twins' split is not -> the 1e-6 bar
+    r2 = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], foldid=fo, inner_ps=ips, inner_out=iout,
+                              n_continuous=d["n_continuous"], expand=2, B=0, thresh=1e-13)
+    o2 = oracle.crossfit_aipw(xd, d["w"], d["y"], fo, ips, iout, thresh=1e-13)
+    if np.allclose(r2["lambda_ps"], o2["lambda_ps"], rtol=1e-9) and np.allclose(r2["lambda_out"], o2["lambda_out"], rtol=1e-9):
+        assert abs(r2["tau"] - o2["tau"]) <= 1e-6 * abs(o2["tau"])
+        assert abs(r2["se_sandwich"] - o2["se"]) <= 1e-6 * o2["se"]
+
+
+def test_crossfit_products_only_design_matches_expand_then_fit(engine, oracle):
+    """expand = 1 (the C1 benchmark's p0^2 products) builds the same design as a2 followed by a
+    plain fit: checked through the outcome/propensity lambdas and tau at the twin-column level."""
+    n, p0 = 2500, 5
+    d = _data(n, p0)
+    fo, ips, iout = make_folds(n)
+    r = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], foldid=fo, inner_ps=ips, inner_out=iout,
+                             n_continuous=d["n_continuous"], expand=1, B=0)
+    xd = oracle.expand_deg2(_scaled(oracle, d), False)
+    o = oracle.crossfit_aipw(xd, d["w"], d["y"], fo, ips, iout)
+    assert np.allclose(r["lambda_out"], o["lambda_out"], rtol=1e-9)
+    assert abs(r["tau"] - o["tau"]) <= 1e-4 * abs(o["tau"])
+
+
+def test_crossfit_device_pointers_equal_host_buffers(engine):
+    import torch
+    n, p0 = 4000, 8
+    d = _data(n, p0)
+    fo, ips, iout = make_folds(n)
+    kw = dict(foldid=fo, inner_ps=ips, inner_out=iout, n_continuous=d["n_continuous"], expand=0, B=50, boot_mode=1, boot_seed=5)
+    h = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], **kw)
+    dev = torch.device("cuda:0")
+    xb = torch.from_numpy(np.asfortranarray(d["x_raw"]).T.copy()).to(dev)      # column-major n x p0
+    w = torch.from_numpy(d["w"]).to(dev); y = torch.from_numpy(d["y"]).to(dev)
+    g = engine.crossfit_aipw(xb.data_ptr(), w.data_ptr(), y.data_ptr(), n=n, p0=p0, on_device=1, **kw)
+    assert g["tau"] == h["tau"] and g["se_sandwich"] == h["se_sandwich"] and g["se_bootstrap"] == h["se_bootstrap"]
+    assert torch.equal(xb, torch.from_numpy(np.asfortranarray(d["x_raw"]).T.copy()).to(dev))   # caller's buffer untouched
+
+
+# ---------------------------------------------------------------- host mirror of ate_functions.R
+def test_r_entry_point_mirrors(engine, oracle):
+    import pandas as pd
+    from ate_replication_causalml_b200 import ate_functions as af
+    n, p0 = 2000, 6
+    d = _data(n, p0)
+    xs = _scaled(oracle, d)
+    names = [f"x{j}" for j in range(p0)]
+    df = pd.DataFrame(xs, columns=names)
+    df["W"] = d["w"]; df["Y"] = d["y"]
+    af.set_engine(engine)
+    af.set_covariates(names)
+    fid = synth.fold_ids(n, 10, 3)
+    # prop_score_lasso: n x 1 matrix of predict(type = "response") at lambda.1se
+    ps = af.prop_score_lasso(df, "W", foldid=fid)
+    oc = oracle.cv_glmnet(xs, d["w"], fid, "binomial")
+    ref = oracle.predict(xs, oc["a0"][oc["idx_1se"]], oc["beta"][:, oc["idx_1se"]], True)
+    assert ps.shape == (n, 1) and np.abs(ps[:, 0] - ref).max() < 1e-9
+    # ate_condmean_lasso / ate_lasso: coefficient of W at lambda.1se, degenerate interval
+    xw = np.column_stack([xs, d["w"]])
+    for fn, pf, label in ((af.ate_condmean_lasso, np.r_[np.ones(p0), 0.0], "Single-equation LASSO"),
+                          (af.ate_lasso, np.ones(p0 + 1), "Usual LASSO")):
+        row = fn(df, "W", "Y", foldid=fid)
+        og = oracle.cv_glmnet(xw, d["y"], fid, "gaussian", penalty_factor=pf)
+        assert list(row.columns) == ["Method", "ATE", "lower_ci", "upper_ci"] and row["Method"][0] == label
+        assert abs(row["ATE"][0] - og["beta"][p0, og["idx_1se"]]) < 1e-9
+        assert row["lower_ci"][0] == row["ATE"][0] == row["upper_ci"][0]
+    # doubly robust tail (ate_functions.R:241-263) and tau_hat_dr_est (:267-283)
+    p = np.clip(ref, 0.02, 0.98); m0 = np.full(n, 0.2); m1 = np.full(n, 0.3)
+    row = af.doubly_robust_scores(d["w"], d["y"], p, m0, m1, method="Doubly Robust with logistic regression PS")
+    t, s = oracle.aipw(d["w"], d["y"], p, m0, m1)
+    assert abs(row["ATE"][0] - t) < 1e-12 and abs(row["upper_ci"][0] - (t + 1.96 * s)) < 1e-10
+    oracle.set_seed(11); idx = oracle.sample_replace(n, n, 1)
+    assert abs(af.tau_hat_dr_est(d["w"], d["y"], p, m0, m1, idx) - oracle.tau_hat_dr_est(d["w"], d["y"], p, m0, m1, idx)) < 1e-12
+    engine.r_set_seed(11)                                    # ... or drawn by the library's own R-compatible stream
+    assert abs(af.tau_hat_dr_est(d["w"], d["y"], p, m0, m1) - oracle.tau_hat_dr_est(d["w"], d["y"], p, m0, m1, idx)) < 1e-12
+    # composite wrapper returns the reference's one-row frame
+    fo, ips, iout = make_folds(n)
+    row = af.crossfit_aipw(df, "W", "Y", bootstrap_se=False, foldid=fo, inner_ps=ips, inner_out=iout)
+    o = oracle.crossfit_aipw(xs, d["w"], d["y"], fo, ips, iout)
+    assert abs(row["ATE"][0] - o["tau"]) <= 1e-9 * abs(o["tau"])
+    assert abs(row["lower_ci"][0] - (o["tau"] - 1.96 * o["se"])) < 1e-9
