@@ -122,7 +122,8 @@ __device__ __forceinline__ void block_sum(double (&v)[NV], double *smem) {
 // row-major design layout: n rows of ld doubles.
 int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t *rows,
                long long row_begin, long long nrows, const double *v, double *G /*p*p*/,
-               long long hole_begin = 0, long long hole_len = 0);
+               long long hole_begin = 0, long long hole_len = 0, const int *colidx = nullptr,
+               int ncload = 0, int ldg = 0);
 int ate_i_transpose_to_rowmajor(ate_ctx *ctx, const double *x_colmajor, long long n, int p,
                                 double *X, long long ld, int col_offset);
 int ate_i_standardize(ate_ctx *ctx, double *d_x, long long n, int p, const int *d_cols, int ncols,

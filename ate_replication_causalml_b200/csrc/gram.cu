@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(G_THREADS, 1)
 gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const int32_t *__restrict__ rows,
                  long long row_begin, long long nrows, long long hole_begin, long long hole_len,
                  long long rows_per_chunk, const double *__restrict__ v, int nblk, int stages,
-                 double *__restrict__ partials) {
+                 const int *__restrict__ colidx, double *__restrict__ partials) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int pitch = ncols + G_PAD;                       // doubles
     const size_t stage_doubles = (size_t)G_ROWS * pitch;
@@ -101,6 +101,8 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
     const int nit = (int)((c_rows + G_ROWS - 1) / G_ROWS);
     const uint32_t row_bytes = (uint32_t)ncols * 8u;
 
+    for (int e = threadIdx.x; e < stages * G_ROWS * G_PAD; e += blockDim.x)
+        sx[(size_t)(e / G_PAD) * pitch + ncols + (e % G_PAD)] = 0.0;
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(full + s, 1);
@@ -112,26 +114,38 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
 
     if (warp == G_CWARPS) {
         // ---------------- producer warp: one staged observation per lane ----------------
+        // The row id and weight of stage it+1 are fetched before waiting for stage it's slot, so
+        // the dependent global loads never sit between "slot free" and "copy issued".
+        const long long c_end = c_begin + c_rows;
+        auto fetch = [&](int it, long long &r, double &vv) -> bool {
+            const long long t = c_begin + (long long)it * G_ROWS + lane;
+            if (t >= c_end) return false;
+            // logical position t skips the hole (the held-out inner fold of a CV fit)
+            const long long tp = row_begin + t + (t >= hole_begin ? hole_len : 0);
+            r = rows ? (long long)__ldg(rows + tp) : tp;
+            vv = v ? __ldg(v + t) : 1.0;
+            return true;
+        };
+        long long cur_r = 0, nxt_r = 0;
+        double cur_v = 0.0, nxt_v = 0.0;
+        bool cur_ok = nit > 0 ? fetch(0, cur_r, cur_v) : false, nxt_ok = false;
         for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
+            nxt_ok = (it + 1 < nit) ? fetch(it + 1, nxt_r, nxt_v) : false;
             mbar_wait(empty + s, ph ^ 1u);
-            const long long t = c_begin + (long long)it * G_ROWS + lane;
-            const bool valid = t < c_begin + c_rows;
             double *dst = sx + stage_doubles * s + (size_t)lane * pitch;
-            sv[s * G_ROWS + lane] = valid ? (v ? __ldg(v + t) : 1.0) : 0.0;
-            if (!valid)
+            sv[s * G_ROWS + lane] = cur_ok ? cur_v : 0.0;
+            if (!cur_ok)
                 for (int c = 0; c < ncols; ++c) dst[c] = 0.0;
-            const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+            const unsigned vmask = __ballot_sync(0xffffffffu, cur_ok);
             __syncwarp();
             if (lane == 0) mbar_arrive_expect_tx(full + s, row_bytes * (uint32_t)__popc(vmask));
             __syncwarp();
-            if (valid) {
-                // logical position t skips the hole (the held-out inner fold of a CV fit)
-                const long long tp = row_begin + t + (t >= hole_begin ? hole_len : 0);
-                const long long r = rows ? (long long)__ldg(rows + tp) : tp;
-                bulk_g2s(dst, X + (size_t)r * (size_t)ld, row_bytes, full + s);
-            }
+            if (cur_ok) bulk_g2s(dst, X + (size_t)cur_r * (size_t)ld, row_bytes, full + s);
+            cur_ok = nxt_ok;
+            cur_r = nxt_r;
+            cur_v = nxt_v;
         }
     } else {
         // ---------------- consumer warps: one 32x32 block of the lower triangle each -----
@@ -145,7 +159,15 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
 #pragma unroll
             for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
         const int g = lane >> 2, k4 = lane & 3;
-        const int offA = bi * 32 + g, offB = bj * 32 + g;
+        // operand columns: the block's own 32 columns, or -- for a column-restricted Gram -- the
+        // design columns the list names (a padded list points at the zeroed pad slot `ncols`)
+        int offA[4], offB[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            const int ia = bi * 32 + m * 8 + g, ib = bj * 32 + m * 8 + g;
+            offA[m] = (colidx && active) ? __ldg(colidx + ia) : ia;
+            offB[m] = (colidx && active) ? __ldg(colidx + ib) : ib;
+        }
         for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
@@ -160,9 +182,9 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
                     const double vv = vs[r];
                     double a[4], b[4];
 #pragma unroll
-                    for (int m = 0; m < 4; ++m) a[m] = rowp[offA + m * 8];
+                    for (int m = 0; m < 4; ++m) a[m] = rowp[offA[m]];
 #pragma unroll
-                    for (int m = 0; m < 4; ++m) b[m] = rowp[offB + m * 8] * vv;
+                    for (int m = 0; m < 4; ++m) b[m] = rowp[offB[m]] * vv;
 #pragma unroll
                     for (int m = 0; m < 4; ++m)
 #pragma unroll
@@ -186,18 +208,31 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
 }
 
 // fold the row chunks in order and scatter into the full symmetric p x p matrix
-__global__ void gram_fold_kernel(const double *__restrict__ partials, int nchunks, int nblk, int p,
-                                 double *__restrict__ G) {
+__global__ void __launch_bounds__(256)
+gram_fold_kernel(const double *__restrict__ partials, int nchunks, int nblk, int p, int ldg,
+                 double *__restrict__ G) {
     const int q = blockIdx.x;
     int bi, bj;
     block_coords(q, bi, bj);
-    for (int e = threadIdx.x; e < 1024; e += blockDim.x) {
-        double s = 0.0;
-        for (int c = 0; c < nchunks; ++c) s += partials[((size_t)c * nblk + q) * 1024 + e];
-        const int r = bi * 32 + (e >> 5), col = bj * 32 + (e & 31);
+    // 4 elements per thread, chunk loop unrolled so the loads of several chunks are in flight;
+    // the additions stay in chunk order (bit-reproducible)
+    const int e = threadIdx.x * 4;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    const double *src = partials + (size_t)q * 1024 + e;
+    const size_t cstride = (size_t)nblk * 1024;
+#pragma unroll 8
+    for (int c = 0; c < nchunks; ++c) {
+        const double4 t = *reinterpret_cast<const double4 *>(src + (size_t)c * cstride);
+        s0 += t.x; s1 += t.y; s2 += t.z; s3 += t.w;
+    }
+    const double sv[4] = {s0, s1, s2, s3};
+    const int r = bi * 32 + (e >> 5);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int col = bj * 32 + (e & 31) + k;
         if (r < p && col < p && col <= r) {
-            G[(size_t)r * p + col] = s;
-            G[(size_t)col * p + r] = s;
+            G[(size_t)r * ldg + col] = sv[k];
+            G[(size_t)col * ldg + r] = sv[k];
         }
     }
 }
@@ -208,18 +243,24 @@ __global__ void gram_fold_kernel(const double *__restrict__ partials, int nchunk
 // and zero beyond the real columns).  rows: device row list or NULL.  v: device weights indexed
 // by position in the list (or NULL).  G: device p*p output.  The nrows logical positions map to
 // list entries row_begin + t, skipping hole_len entries from logical position hole_begin on.
+// Column-restricted form: colidx (device, padded to a multiple of 32 with the value `ncload`) names
+// the p design columns that enter the Gram; `ncload` columns of every row are staged; G is written
+// compactly with leading dimension ldg.  colidx == NULL: columns 0..p-1, ncload = round_up(p, 32).
 int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t *rows,
                long long row_begin, long long nrows, const double *v, double *G, long long hole_begin,
-               long long hole_len) {
+               long long hole_len, const int *colidx, int ncload, int ldg) {
     if (hole_len <= 0) {
         hole_begin = nrows;
         hole_len = 0;
     }
     if (p <= 0 || nrows < 0) return ate_fail(ctx, -1, "gram: bad shape");
-    const int ncols = (p + 31) / 32 * 32;
+    const int pp = (p + 31) / 32 * 32;
+    const int ncols = colidx ? ncload : pp;
+    if (!colidx) ldg = p;
+    if (colidx && (ncload % 2 != 0 || ncload <= 0)) return ate_fail(ctx, -1, "gram: bad ncload");
     if (ncols > ld) return ate_fail(ctx, -1, "gram: ld (%lld) < padded column count (%d)", ld, ncols);
     if ((ld & 1) != 0) return ate_fail(ctx, -1, "gram: ld must be even (16-byte aligned rows)");
-    const int nb = ncols / 32, nblk = nb * (nb + 1) / 2;
+    const int nb = pp / 32, nblk = nb * (nb + 1) / 2;
     const size_t stage_bytes = sizeof(double) * (size_t)G_ROWS * (ncols + G_PAD);
     int stages = (int)((G_SMEM_LIMIT - 1024) / (stage_bytes + G_ROWS * sizeof(double)));
     if (stages > G_MAX_STAGES) stages = G_MAX_STAGES;
@@ -251,16 +292,16 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
         ATE_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     }
     gram_dmma_kernel<<<dim3(ngroups, nchunks), G_THREADS, smem, ctx->stream>>>(
-        X, ld, ncols, rows, row_begin, nrows, hole_begin, hole_len, rpc, v, nblk, stages, (double *)scr);
+        X, ld, ncols, rows, row_begin, nrows, hole_begin, hole_len, rpc, v, nblk, stages, colidx, (double *)scr);
     ATE_LAUNCHED(ctx);
     if (ctx->profile) {
         ATE_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
         ctx->prof_events.emplace_back(e0, e1);
         ctx->prof_launches++;
         ctx->prof_flops += (double)nrows * p * (p + 1.0);
-        ctx->prof_bytes += (double)nrows * (p + 1.0) * 8.0;
+        ctx->prof_bytes += (double)nrows * (ncols + 1.0) * 8.0;  // whole staged rows + the weight
     }
-    gram_fold_kernel<<<nblk, 256, 0, ctx->stream>>>((const double *)scr, nchunks, nblk, p, G);
+    gram_fold_kernel<<<nblk, 256, 0, ctx->stream>>>((const double *)scr, nchunks, nblk, p, ldg, G);
     ATE_LAUNCHED(ctx);
     return 0;
 }

@@ -10,11 +10,15 @@
 //                        One warp per observation row, rows read once (HBM-bound).
 //   gram.cu            : H = X^T V X on the DMMA pipe (tensor-bound, the dominant cost).
 // and the coordinate descent then runs on the p x p quadratic:
-//   lognet_cd_kernel   : one CTA per fit.  Standardises H in place (lstandard1's centring and
-//                        1/N scaling are affine in H, X^T v, sum v), then follows lognet2n's
-//                        loop order exactly -- strong-set sweep, intercept step, active-set
-//                        loop -- with g_k = <r, x_k> kept current by covariance updates
-//                        g -= d * H[:,k].  In exact arithmetic the iterates equal glmnet's.
+//   lognet_pre_kernel  : one CTA per fit: convergence test of the previous quadratic, KKT check,
+//                        recording / advancing lambda, strong-rule update.  Only the strong
+//                        set's columns enter the Gram (on average ~1/6 of p at C1, i.e. ~4 % of
+//                        the flops), so this runs BEFORE the Gram pass and hands it the list.
+//   lognet_solve_kernel: one CTA per fit.  Standardises the compact H in place (lstandard1's
+//                        centring and 1/N scaling are affine in H, X^T v, sum v), then follows
+//                        lognet2n's loop order exactly -- strong-set sweep, intercept step,
+//                        active-set loop -- with g_k = <r, x_k> kept current by covariance
+//                        updates g -= d * H[:,k].  In exact arithmetic the iterates equal glmnet's.
 // All fits of a batch (the full-data fits of every outer fold, then all their CV folds) advance
 // one IRLS step per round; finished fits drop out.  The host reads one small flag vector per
 // round.
@@ -26,14 +30,14 @@ namespace {
 
 enum { PH_INIT = 0, PH_REFRESH = 1 };
 enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_SUMS, SD_SUMS2, SD_SUMA, SD_N };
-enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_N };
-// sums layout: gr[ni], hx[ni], then XMZ, SR, DEV
+enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_N };
+// sums layout: gr[ni] = X^T r, hx[ni] = X^T v, hxx[ni] = sum v x^2, then XMZ, SR, DEV
 enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
 
 struct LognetFit {
     const int32_t *list;  // row ids (NULL = identity)
     long long nt, hole_begin, hole_len;
-    int ni, iy, owned;
+    int ni, iy, owned, ldh;
     const double *vp;
     double flmin;
     const double *ulam;
@@ -41,12 +45,12 @@ struct LognetFit {
     int nlam;
     double thr;
     int maxit;
-    double *v, *r;    // [nt]
-    double *H;        // ni x ni
-    double *sums;     // 2 ni + SU_N
+    double *v;        // [nt] IRLS weights of the current step
+    double *H;        // ldh x ldh: X_S^T V X_S over the strong set, in order of entry
+    double *sums;     // 3 ni + SU_N
     double *coef;     // ni + 1 (a0 last): raw-scale coefficients for the next eval
     double *st_d;     // b, bs, xv, ga, xm, xs, vq [7 ni] + SD_N
-    int *st_i;        // ixx, mm, mlist, ju [4 ni] + SI_N
+    int *st_i;        // ixx, mm, mlist, ju, spos [5 ni] + slist [ldh] + SI_N
     double *alm, *a0, *dev, *beta;  // outputs
 };
 
@@ -56,46 +60,63 @@ constexpr int CD_THREADS = 256;
 __device__ __forceinline__ long long phys_pos(const LognetFit &f, long long t) {
     return t + (t >= f.hole_begin ? f.hole_len : 0);
 }
+__device__ __forceinline__ int *fit_slist(const LognetFit &f) { return f.st_i + 5 * (size_t)f.ni; }
+__device__ __forceinline__ int *fit_scal_i(const LognetFit &f) { return f.st_i + 5 * (size_t)f.ni + f.ldh; }
+__device__ __forceinline__ double *fit_scal_d(const LognetFit &f) { return f.st_d + 7 * (size_t)f.ni; }
 
 // ---- per-row pass -------------------------------------------------------------------------
+// One warp per observation; the next row's loads are issued before the current row is reduced so
+// that two rows (4 KB at p = 256) are in flight per warp.
 template <int ITER>
 __global__ void __launch_bounds__(EV_THREADS)
 lognet_eval_kernel(const LognetFit *__restrict__ fits, int fid, const double *__restrict__ X,
                    long long ld, double *__restrict__ partials) {
     const LognetFit f = fits[fid];
-    extern __shared__ double sm[];  // [warps][2*ni + SU_N]
+    extern __shared__ double sm[];  // [warps][3*ni + SU_N]
     const int ni = f.ni;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const int plen = 2 * ni + SU_N;
-    double beta[2 * ITER], gr[2 * ITER], hx[2 * ITER];
+    const int plen = 3 * ni + SU_N;
+    double beta[2 * ITER], gr[2 * ITER], hx[2 * ITER], hxx[2 * ITER];
 #pragma unroll
     for (int i = 0; i < ITER; ++i) {
         const int c = 2 * lane + 64 * i;
         beta[2 * i] = c < ni ? f.coef[c] : 0.0;
         beta[2 * i + 1] = c + 1 < ni ? f.coef[c + 1] : 0.0;
-        gr[2 * i] = gr[2 * i + 1] = hx[2 * i] = hx[2 * i + 1] = 0.0;
+        gr[2 * i] = gr[2 * i + 1] = hx[2 * i] = hx[2 * i + 1] = hxx[2 * i] = hxx[2 * i + 1] = 0.0;
     }
     const double a0 = f.coef[ni];
     const double w = 1.0 / (double)f.nt;
     const double pmin = GLM_PMIN, fmax_ = log(1.0 / pmin - 1.0), fmin_ = -fmax_;
     double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0;
     const long long wstride = (long long)gridDim.x * nw;
-    for (long long t = (long long)blockIdx.x * nw + wid; t < f.nt; t += wstride) {
-        const long long pp = phys_pos(f, t);
+    long long t = (long long)blockIdx.x * nw + wid;
+    double xn[2 * ITER];
+    double yn = 0.0;
+    auto load_row = [&](long long tt) {
+        const long long pp = phys_pos(f, tt);
         const long long row = f.list ? (long long)__ldg(f.list + pp) : pp;
         const double *xr = X + (size_t)row * (size_t)ld;
-        double x[2 * ITER];
-        double dot = 0.0;
 #pragma unroll
         for (int i = 0; i < ITER; ++i) {
             const int c = 2 * lane + 64 * i;
             double2 t2 = make_double2(0.0, 0.0);
             if (c + 1 < ld) t2 = __ldg(reinterpret_cast<const double2 *>(xr + c));
-            x[2 * i] = t2.x;
-            x[2 * i + 1] = t2.y;
-            dot += t2.x * beta[2 * i] + t2.y * beta[2 * i + 1];
+            xn[2 * i] = t2.x;
+            xn[2 * i + 1] = t2.y;
         }
-        const double yi = __ldg(xr + f.iy);
+        yn = __ldg(xr + f.iy);
+    };
+    if (t < f.nt) load_row(t);
+    for (; t < f.nt; t += wstride) {
+        double x[2 * ITER];
+        double dot = 0.0;
+#pragma unroll
+        for (int i = 0; i < 2 * ITER; ++i) {
+            x[i] = xn[i];
+            dot += x[i] * beta[i];
+        }
+        const double yi = yn;
+        if (t + wstride < f.nt) load_row(t + wstride);
         const double fi = a0 + warp_sum(dot);
         double q;
         if (fi < fmin_)
@@ -107,7 +128,6 @@ lognet_eval_kernel(const LognetFit *__restrict__ fits, int fid, const double *__
         const double vi = w * q * (1.0 - q), ri = w * (yi - q);
         if (lane == 0) {
             f.v[t] = vi;
-            f.r[t] = ri;
             const double qc = fmin(fmax(q, pmin), 1.0 - pmin);
             s_xmz += vi;
             s_sr += ri;
@@ -115,27 +135,29 @@ lognet_eval_kernel(const LognetFit *__restrict__ fits, int fid, const double *__
         }
 #pragma unroll
         for (int i = 0; i < 2 * ITER; ++i) {
+            const double vx = vi * x[i];
             gr[i] += ri * x[i];
-            hx[i] += vi * x[i];
+            hx[i] += vx;
+            hxx[i] += vx * x[i];
         }
     }
     double *mine = sm + (size_t)wid * plen;
 #pragma unroll
     for (int i = 0; i < ITER; ++i) {
-        const int c = 2 * lane + 64 * i;
-        if (c < ni) {
-            mine[c] = gr[2 * i];
-            mine[ni + c] = hx[2 * i];
-        }
-        if (c + 1 < ni) {
-            mine[c + 1] = gr[2 * i + 1];
-            mine[ni + c + 1] = hx[2 * i + 1];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int c = 2 * lane + 64 * i + h;
+            if (c < ni) {
+                mine[c] = gr[2 * i + h];
+                mine[ni + c] = hx[2 * i + h];
+                mine[2 * ni + c] = hxx[2 * i + h];
+            }
         }
     }
     if (lane == 0) {
-        mine[2 * ni + SU_XMZ] = s_xmz;
-        mine[2 * ni + SU_SR] = s_sr;
-        mine[2 * ni + SU_DEV] = s_dev;
+        mine[3 * ni + SU_XMZ] = s_xmz;
+        mine[3 * ni + SU_SR] = s_sr;
+        mine[3 * ni + SU_DEV] = s_dev;
     }
     __syncthreads();
     for (int e = threadIdx.x; e < plen; e += blockDim.x) {
@@ -145,13 +167,16 @@ lognet_eval_kernel(const LognetFit *__restrict__ fits, int fid, const double *__
     }
 }
 
-__global__ void fold_partials_kernel(const double *__restrict__ partials, int nparts, int len,
-                                     double *__restrict__ out) {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+// one warp per output element, partials folded in a fixed (lane-strided, then butterfly) order
+__global__ void __launch_bounds__(256)
+fold_partials_kernel(const double *__restrict__ partials, int nparts, int len, double *__restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (e >= len) return;
     double s = 0.0;
-    for (int q = 0; q < nparts; ++q) s += partials[(size_t)q * len + e];
-    out[e] = s;
+    for (int q = lane; q < nparts; q += 32) s += partials[(size_t)q * len + e];
+    s = warp_sum(s);
+    if (lane == 0) out[e] = s;
 }
 
 // sum of the response column over the fit's rows -> q0, bz; arms the first eval
@@ -171,8 +196,8 @@ lognet_init_kernel(const LognetFit *__restrict__ fits, const double *__restrict_
         const double q0 = acc[0] / (double)f.nt;
         const double bz = log(q0 / (1.0 - q0));
         f.coef[f.ni] = bz;
-        double *sd = f.st_d + 7 * (size_t)f.ni;
-        int *si = f.st_i + 4 * (size_t)f.ni;
+        double *sd = fit_scal_d(f);
+        int *si = fit_scal_i(f);
         for (int k = 0; k < SD_N; ++k) sd[k] = 0.0;
         for (int k = 0; k < SI_N; ++k) si[k] = 0;
         sd[SD_Q0] = q0;
@@ -214,41 +239,51 @@ __device__ __forceinline__ double bmax_all(double v, double *red) {
     return t;
 }
 
-// ---- one IRLS round of coordinate descent per fit -------------------------------------------
+// ---- IRLS round, part 1: bookkeeping that needs only the evaluation pass --------------------
+// Convergence of the previous quadratic, KKT re-check, recording lambda, advancing it, and the
+// strong-set update.  Leaves the (padded) strong-column list for the Gram pass and tells the host
+// how many columns it holds.  flags_out[3*fit + {0,1,2}] = {done, nS, solve pending}.
 __global__ void __launch_bounds__(CD_THREADS)
-lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flags) {
+lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_out) {
     const LognetFit f = fits[blockIdx.x];
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x;
-    int *si = f.st_i + 4 * (size_t)ni;
-    double *sd = f.st_d + 7 * (size_t)ni;
+    int *si = fit_scal_i(f);
+    double *sd = fit_scal_d(f);
     if (si[SI_DONE]) {
-        if (tid == 0) done_flags[blockIdx.x] = 1;
+        if (tid == 0) {
+            flags_out[3 * blockIdx.x] = 1;
+            flags_out[3 * blockIdx.x + 1] = 0;
+            flags_out[3 * blockIdx.x + 2] = 0;
+            si[SI_SOLVE] = 0;
+        }
         return;
     }
     extern __shared__ double sm[];
-    double *b = sm, *g = b + ni, *hxs = g + ni, *xv = hxs + ni, *vq = xv + ni, *red = vq + ni;  // red[32]
-    int *ixx = reinterpret_cast<int *>(red + 32), *mm = ixx + ni, *ml = mm + ni, *ju = ml + ni;
+    double *g = sm, *red = g + ni;  // red[32]
     double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gga = Gxv + ni, *Gxm = Gga + ni,
            *Gxs = Gxm + ni, *Gvq = Gxs + ni;
-    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni;
-    double *H = f.H;
-    const double *gr = f.sums, *hx = f.sums + ni;
-    const double xmz = f.sums[2 * ni + SU_XMZ], sr_in = f.sums[2 * ni + SU_SR];
-    const double devsum = f.sums[2 * ni + SU_DEV];
+    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni;
+    int *slist = fit_slist(f);
+    const double *gr = f.sums, *hx = f.sums + ni, *hxx = f.sums + 2 * ni;
+    const double xmz = f.sums[3 * ni + SU_XMZ], sr_in = f.sums[3 * ni + SU_SR];
+    const double devsum = f.sums[3 * ni + SU_DEV];
     const double pmin = GLM_PMIN, vmin = (1.0 + pmin) * pmin * (1.0 - pmin);
 
-    int nin = si[SI_NIN], ilm = si[SI_ILM], nlp = si[SI_NLP];
+    int ilm = si[SI_ILM], nS = si[SI_NS];
+    const int nin = si[SI_NIN];
     const int phase = si[SI_PHASE];
-    double b0 = sd[SD_B0], al = sd[SD_AL], al0 = sd[SD_AL0];
+    const double b0 = sd[SD_B0];
+    double al = sd[SD_AL], al0 = sd[SD_AL0];
     const int nlam = (f.flmin < 1.0) ? f.nlam : min(f.nlam, *f.nlam_ptr);
     const int mnl = min(GLM_MNLAM, nlam);
+    double dev0 = sd[SD_DEV0], dev1 = sd[SD_DEV1], shr = sd[SD_SHR], alf = sd[SD_ALF];
 
     if (phase == PH_INIT) {
         // lstandard1 from the first pass (v = w q0 (1 - q0) is constant there)
         double vs = 0.0;
         for (int j = tid; j < ni; j += T) {
             const double m = hx[j] / xmz;
-            const double sq = H[(size_t)j * ni + j] / xmz;
+            const double sq = hxx[j] / xmz;
             const double var = sq - m * m;
             const bool ok = var > 1.0e-14 * (sq > 1.0e-300 ? sq : 1.0e-300);
             Gxm[j] = m;
@@ -263,34 +298,17 @@ lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flag
             Gixx[j] = 0;
             Gmm[j] = 0;
             Gml[j] = 0;
+            Gspos[j] = -1;
         }
+        for (int c = tid; c < f.ldh; c += T) slist[c] = f.ldh;  // sentinel: the Gram kernel's zero slot
         vs = bsum_all(vs, red);
         for (int j = tid; j < ni; j += T) Gvq[j] = Gvq[j] * (double)ni / vs;
         __syncthreads();
     }
-    // ---- state into shared memory; standardise this round's moments ----
-    for (int j = tid; j < ni; j += T) {
-        b[j] = Gb[j];
-        vq[j] = Gvq[j];
-        ixx[j] = Gixx[j];
-        mm[j] = Gmm[j];
-        ml[j] = Gml[j];
-        ju[j] = Gju[j];
-        const double m = Gxm[j], s = Gxs[j];
-        g[j] = ju[j] ? (gr[j] - m * sr_in) / s : 0.0;
-        hxs[j] = ju[j] ? (hx[j] - m * xmz) / s : 0.0;
-    }
+    // gradient of the refreshed quadratic on standardised columns: g_j = <r, x_j>
+    for (int j = tid; j < ni; j += T) g[j] = Gju[j] ? (gr[j] - Gxm[j] * sr_in) / Gxs[j] : 0.0;
     __syncthreads();
-    for (int e = tid; e < ni * ni; e += T) {
-        const int r = e / ni, c = e - r * ni;
-        const double mr = Gxm[r], mc = Gxm[c];
-        H[e] = (H[e] - mr * hx[c] - mc * hx[r] + mr * mc * xmz) / (Gxs[r] * Gxs[c]);
-    }
-    __syncthreads();
-    double sr = sr_in;
-    double dev0 = sd[SD_DEV0], dev1 = sd[SD_DEV1], shr = sd[SD_SHR], alf = sd[SD_ALF];
     bool begin_lambda = false, finished = false;
-    int jerr = 0;
 
     if (phase == PH_INIT) {
         const double q0 = sd[SD_Q0], bz = sd[SD_BZ];
@@ -298,21 +316,21 @@ lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flag
         dev0 = dev1;  // y is 0/1: the y log y terms vanish
         shr = f.thr * dev0;
         alf = (f.flmin < 1.0) ? pow(fmax(GLM_EPS, f.flmin), 1.0 / (double)(nlam - 1)) : 1.0;
-        for (int j = tid; j < ni; j += T) Gga[j] = ju[j] ? fabs(g[j]) : 0.0;
+        for (int j = tid; j < ni; j += T) Gga[j] = Gju[j] ? fabs(g[j]) : 0.0;
         __syncthreads();
         ilm = 0;
         al = 0.0;
         begin_lambda = true;
     } else {
         // ---- the quadratic was just refreshed at the new coefficients: converged? ----
-        bool stop_path = (xmz <= vmin);
+        const bool stop_path = (xmz <= vmin);
         bool again = false;
         if (!stop_path) {
             const double d0 = b0 - sd[SD_BS0];
             int moved = (xmz * d0 * d0 >= shr) ? 1 : 0;
             for (int l = tid; l < nin; l += T) {
-                const int k = ml[l];
-                const double d = b[k] - Gbs[k];
+                const int k = Gml[l];
+                const double d = Gb[k] - Gbs[k];
                 if (Gxv[k] * d * d >= shr) moved = 1;
             }
             moved = __syncthreads_or(moved);
@@ -320,13 +338,12 @@ lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flag
                 again = true;
             else {
                 int add = 0;
-                const double al1 = al;
                 for (int k = tid; k < ni; k += T) {
-                    if (ixx[k] || !ju[k]) continue;
+                    if (Gixx[k] || !Gju[k]) continue;
                     const double ga = fabs(g[k]);
                     Gga[k] = ga;
-                    if (ga > al1 * vq[k]) {
-                        ixx[k] = 1;
+                    if (ga > al * Gvq[k]) {
+                        Gixx[k] = 2;  // newly strong: appended to the list below
                         add = 1;
                     }
                 }
@@ -338,10 +355,10 @@ lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flag
             double part = 0.0;
             int nz = 0;
             for (int j = tid; j < ni; j += T) {
-                const double bj = (b[j] != 0.0) ? b[j] / Gxs[j] : 0.0;
+                const double bj = (Gb[j] != 0.0) ? Gb[j] / Gxs[j] : 0.0;
                 f.beta[(size_t)ilm * ni + j] = bj;
                 part += bj * Gxm[j];
-                nz += (b[j] != 0.0);
+                nz += (Gb[j] != 0.0);
             }
             const double dotbm = bsum_all(part, red);
             const int me = (int)bsum_all((double)nz, red);
@@ -377,155 +394,205 @@ lognet_cd_kernel(const LognetFit *__restrict__ fits, int *__restrict__ done_flag
         else {
             double t = 0.0;
             for (int j = tid; j < ni; j += T)
-                if (ju[j] && vq[j] > 0.0) t = fmax(t, Gga[j] / vq[j]);
+                if (Gju[j] && Gvq[j] > 0.0) t = fmax(t, Gga[j] / Gvq[j]);
             al0 = bmax_all(t, red);
             al = alf * al0;
         }
         const double tlam = 2.0 * al - al0;
         for (int k = tid; k < ni; k += T)
-            if (!ixx[k] && ju[k] && Gga[k] > tlam * vq[k]) ixx[k] = 1;
-        __syncthreads();
+            if (!Gixx[k] && Gju[k] && Gga[k] > tlam * Gvq[k]) Gixx[k] = 2;
     }
-    if (!finished) {
-        // ---- solve the penalised quadratic for the current lambda (lognet2n inner loops) ----
-        const double al1 = al;
-        {   // statistics: size of the strong set this round (what a column-restricted Gram would need)
-            int cs = 0;
-            for (int j = tid; j < ni; j += T) cs += ixx[j];
-            const double ns = bsum_all((double)cs, red);
-            if (tid == 0) {
-                sd[SD_SUMS] += ns;
-                sd[SD_SUMS2] += ns * ns;
-                sd[SD_SUMA] += (double)nin;
-            }
-        }
-        if (tid == 0) sd[SD_BS0] = b0;
-        for (int j = tid; j < ni; j += T) {
-            Gbs[j] = b[j];
-            xv[j] = H[(size_t)j * ni + j];
-            Gxv[j] = xv[j];
-        }
-        __syncthreads();
-        bool fail = false;
-        for (;;) {
-            ++nlp;
-            double dlx = 0.0;
-            for (int k = 0; k < ni; ++k) {
-                if (!ixx[k]) continue;
-                const double bk = b[k], gk = g[k], xk = xv[k];
-                const double u = gk + xk * bk, au = fabs(u) - vq[k] * al1;
-                const double bn = au <= 0.0 ? 0.0 : copysign(au, u) / xk;
-                const double d = bn - bk;
-                if (fabs(d) <= 0.0) continue;
-                dlx = fmax(dlx, xk * d * d);
-                const bool fresh = (mm[k] == 0);
-                if (fresh) ++nin;
-                sr -= d * hxs[k];
-                __syncthreads();
-                if (tid == 0) {
-                    b[k] = bn;
-                    if (fresh) {
-                        mm[k] = nin;
-                        ml[nin - 1] = k;
-                    }
-                }
-                const double *hk = H + (size_t)k * ni;
-                for (int j = tid; j < ni; j += T) g[j] -= d * hk[j];
-                __syncthreads();
-            }
-            {
-                const double d = sr / xmz;
-                if (d != 0.0) {
-                    b0 += d;
-                    dlx = fmax(dlx, xmz * d * d);
-                    __syncthreads();
-                    for (int j = tid; j < ni; j += T) g[j] -= d * hxs[j];
-                    sr -= d * xmz;
-                    __syncthreads();
-                }
-            }
-            if (dlx < shr) break;
-            if (nlp > f.maxit) {
-                fail = true;
-                break;
-            }
-            for (;;) {
-                ++nlp;
-                dlx = 0.0;
-                for (int l = 0; l < nin; ++l) {
-                    const int k = ml[l];
-                    const double bk = b[k], gk = g[k], xk = xv[k];
-                    const double u = gk + xk * bk, au = fabs(u) - vq[k] * al1;
-                    const double bn = au <= 0.0 ? 0.0 : copysign(au, u) / xk;
-                    const double d = bn - bk;
-                    if (fabs(d) <= 0.0) continue;
-                    dlx = fmax(dlx, xk * d * d);
-                    sr -= d * hxs[k];
-                    __syncthreads();
-                    if (tid == 0) b[k] = bn;
-                    const double *hk = H + (size_t)k * ni;
-                    for (int j = tid; j < ni; j += T) g[j] -= d * hk[j];
-                    __syncthreads();
-                }
-                const double d = sr / xmz;
-                if (d != 0.0) {
-                    b0 += d;
-                    dlx = fmax(dlx, xmz * d * d);
-                    __syncthreads();
-                    for (int j = tid; j < ni; j += T) g[j] -= d * hxs[j];
-                    sr -= d * xmz;
-                    __syncthreads();
-                }
-                if (dlx < shr) break;
-                if (nlp > f.maxit) {
-                    fail = true;
-                    break;
-                }
-            }
-            if (fail) break;
-        }
-        if (fail) {
-            jerr = -(ilm + 1);
-            finished = true;
-        }
-        // ---- coefficients for the next evaluation pass, on the raw x scale ----
-        double part = 0.0;
-        for (int j = tid; j < ni; j += T) {
-            const double bj = (b[j] != 0.0) ? b[j] / Gxs[j] : 0.0;
-            f.coef[j] = bj;
-            part += bj * Gxm[j];
-        }
-        const double dotbm = bsum_all(part, red);
-        if (tid == 0) f.coef[ni] = b0 - dotbm;
-    }
-    // ---- state back to global ----
-    for (int j = tid; j < ni; j += T) {
-        Gb[j] = b[j];
-        Gixx[j] = ixx[j];
-        Gmm[j] = mm[j];
-        Gml[j] = ml[j];
-    }
+    __syncthreads();
     if (tid == 0) {
-        sd[SD_B0] = b0;
+        // newly strong columns join the Gram's column list in ascending order (deterministic)
+        for (int k = 0; k < ni; ++k)
+            if (Gixx[k] == 2) {
+                Gixx[k] = 1;
+                Gspos[k] = nS;
+                slist[nS++] = k;
+            }
         sd[SD_AL] = al;
         sd[SD_AL0] = al0;
         sd[SD_DEV0] = dev0;
         sd[SD_DEV1] = dev1;
         sd[SD_SHR] = shr;
         sd[SD_ALF] = alf;
-        si[SI_NIN] = nin;
         si[SI_ILM] = ilm;
-        si[SI_NLP] = nlp;
+        si[SI_NS] = nS;
         si[SI_PHASE] = PH_REFRESH;
-        si[SI_ROUNDS] += 1;
-        if (jerr) si[SI_JERR] = jerr;
+        si[SI_SOLVE] = finished ? 0 : 1;
         if (finished) {
             si[SI_DONE] = 1;
             // fix.lam: lambda[1] was `big`; R rewrites it by log-linear extrapolation before the
             // sequence is handed to the CV folds
             if (f.flmin < 1.0 && si[SI_LMU] > 2) f.alm[0] = exp(2.0 * log(f.alm[1]) - log(f.alm[2]));
         }
-        done_flags[blockIdx.x] = finished ? 1 : 0;
+        flags_out[3 * blockIdx.x] = finished ? 1 : 0;
+        flags_out[3 * blockIdx.x + 1] = nS;
+        flags_out[3 * blockIdx.x + 2] = finished ? 0 : 1;
+    }
+}
+
+// ---- IRLS round, part 2: solve the penalised quadratic on the strong set -------------------
+__global__ void __launch_bounds__(CD_THREADS)
+lognet_solve_kernel(const LognetFit *__restrict__ fits) {
+    const LognetFit f = fits[blockIdx.x];
+    const int ni = f.ni, tid = threadIdx.x, T = blockDim.x, ldh = f.ldh;
+    int *si = fit_scal_i(f);
+    double *sd = fit_scal_d(f);
+    if (si[SI_DONE] || !si[SI_SOLVE]) return;
+    extern __shared__ double sm[];
+    double *b = sm, *g = b + ni, *hxs = g + ni, *xv = hxs + ni, *vq = xv + ni, *red = vq + ni;  // red[32]
+    int *ixx = reinterpret_cast<int *>(red + 32), *mm = ixx + ni, *ml = mm + ni, *spos = ml + ni,
+        *sl = spos + ni;
+    double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gxm = Gxv + 2 * ni, *Gxs = Gxm + ni,
+           *Gvq = Gxs + ni;
+    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni;
+    const int *slist = fit_slist(f);
+    double *H = f.H;
+    const double *gr = f.sums, *hx = f.sums + ni, *hxx = f.sums + 2 * ni;
+    const double xmz = f.sums[3 * ni + SU_XMZ], sr_in = f.sums[3 * ni + SU_SR];
+    const int nS = si[SI_NS], ilm = si[SI_ILM];
+    int nin = si[SI_NIN], nlp = si[SI_NLP];
+    double b0 = sd[SD_B0];
+    const double al1 = sd[SD_AL], shr = sd[SD_SHR];
+
+    for (int j = tid; j < ni; j += T) {
+        const double m = Gxm[j], s = Gxs[j];
+        const bool ok = Gju[j] != 0;
+        b[j] = Gb[j];
+        vq[j] = Gvq[j];
+        ixx[j] = Gixx[j];
+        mm[j] = Gmm[j];
+        ml[j] = Gml[j];
+        spos[j] = Gspos[j];
+        g[j] = ok ? (gr[j] - m * sr_in) / s : 0.0;
+        hxs[j] = ok ? (hx[j] - m * xmz) / s : 0.0;
+        // curvature of the standardised column: sum v (x - m)^2 / s^2
+        const double xvj = ok ? (hxx[j] - 2.0 * m * hx[j] + m * m * xmz) / (s * s) : 0.0;
+        xv[j] = xvj;
+        Gbs[j] = b[j];
+        Gxv[j] = xvj;
+    }
+    for (int c = tid; c < nS; c += T) sl[c] = slist[c];
+    __syncthreads();
+    // standardise the compact Gram in place: lstandard1's centring and scaling are affine in it
+    for (int e = tid; e < nS * nS; e += T) {
+        const int a = e / nS, c = e - a * nS;
+        const int ja = sl[a], jc = sl[c];
+        const double ma = Gxm[ja], mc = Gxm[jc];
+        double *h = H + (size_t)a * ldh + c;
+        *h = (*h - ma * hx[jc] - mc * hx[ja] + ma * mc * xmz) / (Gxs[ja] * Gxs[jc]);
+    }
+    {   // statistics: size of the strong set (what the column-restricted Gram had to cover)
+        if (tid == 0) {
+            sd[SD_SUMS] += (double)nS;
+            sd[SD_SUMS2] += (double)nS * nS;
+            sd[SD_SUMA] += (double)nin;
+            sd[SD_BS0] = b0;
+        }
+    }
+    __syncthreads();
+    double sr = sr_in;
+    bool fail = false;
+    for (;;) {
+        ++nlp;
+        double dlx = 0.0;
+        for (int k = 0; k < ni; ++k) {  // the strong set, in ascending column order as glmnet does
+            if (!ixx[k]) continue;
+            const double bk = b[k], gk = g[k], xk = xv[k];
+            const double u = gk + xk * bk, au = fabs(u) - vq[k] * al1;
+            const double bn = au <= 0.0 ? 0.0 : copysign(au, u) / xk;
+            const double d = bn - bk;
+            if (fabs(d) <= 0.0) continue;
+            dlx = fmax(dlx, xk * d * d);
+            const bool fresh = (mm[k] == 0);
+            if (fresh) ++nin;
+            sr -= d * hxs[k];
+            __syncthreads();
+            if (tid == 0) {
+                b[k] = bn;
+                if (fresh) {
+                    mm[k] = nin;
+                    ml[nin - 1] = k;
+                }
+            }
+            const double *hk = H + (size_t)spos[k] * ldh;
+            for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hk[c];
+            __syncthreads();
+        }
+        {
+            const double d = sr / xmz;
+            if (d != 0.0) {
+                b0 += d;
+                dlx = fmax(dlx, xmz * d * d);
+                __syncthreads();
+                for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hxs[sl[c]];
+                sr -= d * xmz;
+                __syncthreads();
+            }
+        }
+        if (dlx < shr) break;
+        if (nlp > f.maxit) {
+            fail = true;
+            break;
+        }
+        for (;;) {
+            ++nlp;
+            dlx = 0.0;
+            for (int l = 0; l < nin; ++l) {
+                const int k = ml[l];
+                const double bk = b[k], gk = g[k], xk = xv[k];
+                const double u = gk + xk * bk, au = fabs(u) - vq[k] * al1;
+                const double bn = au <= 0.0 ? 0.0 : copysign(au, u) / xk;
+                const double d = bn - bk;
+                if (fabs(d) <= 0.0) continue;
+                dlx = fmax(dlx, xk * d * d);
+                sr -= d * hxs[k];
+                __syncthreads();
+                if (tid == 0) b[k] = bn;
+                const double *hk = H + (size_t)spos[k] * ldh;
+                for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hk[c];
+                __syncthreads();
+            }
+            const double d = sr / xmz;
+            if (d != 0.0) {
+                b0 += d;
+                dlx = fmax(dlx, xmz * d * d);
+                __syncthreads();
+                for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hxs[sl[c]];
+                sr -= d * xmz;
+                __syncthreads();
+            }
+            if (dlx < shr) break;
+            if (nlp > f.maxit) {
+                fail = true;
+                break;
+            }
+        }
+        if (fail) break;
+    }
+    // ---- coefficients for the next evaluation pass, on the raw x scale ----
+    double part = 0.0;
+    for (int j = tid; j < ni; j += T) {
+        const double bj = (b[j] != 0.0) ? b[j] / Gxs[j] : 0.0;
+        f.coef[j] = bj;
+        part += bj * Gxm[j];
+        Gb[j] = b[j];
+        Gmm[j] = mm[j];
+        Gml[j] = ml[j];
+    }
+    const double dotbm = bsum_all(part, red);
+    if (tid == 0) {
+        f.coef[ni] = b0 - dotbm;
+        sd[SD_B0] = b0;
+        si[SI_NIN] = nin;
+        si[SI_NLP] = nlp;
+        si[SI_ROUNDS] += 1;
+        if (fail) {
+            si[SI_JERR] = -(ilm + 1);
+            si[SI_DONE] = 1;
+        }
     }
 }
 
@@ -538,7 +605,7 @@ lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, const double *_
     const LognetFit f = fits[fid];
     extern __shared__ double sm[];  // beta chunk [LC][ni] + a0[LC] + red [warps][LC]
     const int ni = f.ni;
-    const int lmu = f.st_i[4 * (size_t)ni + SI_LMU];
+    const int lmu = fit_scal_i(f)[SI_LMU];
     const int m0 = blockIdx.y * LC;
     const int mc = max(0, min(LC, lmu - m0));
     double *sb = sm, *sa0 = sb + (size_t)LC * ni, *sred = sa0 + LC;
@@ -679,8 +746,6 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     for (auto &pr : probs)
         if (pr.nseg != F) return ate_fail(ctx, -1, "cv_binomial: problems must share nfolds");
     const int nlead = P, nfol = P * F, nfits = nlead + nfol;
-    const size_t n2 = (size_t)ni * ni;
-
     // ---- buffers ----
     size_t vr_total = 0;
     std::vector<size_t> vr_off(nfits);
@@ -696,25 +761,29 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     }
     for (int id = 0; id < nfits; ++id) {
         vr_off[id] = vr_total;
-        vr_total += 2 * (size_t)fit_nt[id];
+        vr_total += (size_t)fit_nt[id];
     }
-    const int plen = 2 * ni + SU_N;
-    const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 4 * (size_t)ni + SI_N;
+    const int plen = 3 * ni + SU_N;
+    const int ldh = (ni + 31) / 32 * 32;
+    if (ldh > ld) return ate_fail(ctx, -1, "cv_binomial: design ld (%lld) < padded feature count (%d)", ld, ldh);
+    const size_t h2 = (size_t)ldh * ldh;
+    const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 5 * (size_t)ni + ldh + SI_N;
+    const size_t si_scal = 5 * (size_t)ni + ldh;
     const size_t out_len = 3 * (size_t)nlam + (size_t)ni * nlam;
     DevBuf<double> dvr, dH, dsums, dcoef, dstd, dout, dvp, dulam, dpart;
     DevBuf<int> dsti, ddone, dnl;
     DevBuf<LognetFit> dfits;
     ATE_CUDA(ctx, dvr.alloc(vr_total));
-    ATE_CUDA(ctx, dH.alloc(n2 * nfits));
+    ATE_CUDA(ctx, dH.alloc(h2 * nfits));
     ATE_CUDA(ctx, dsums.alloc((size_t)plen * nfits));
     ATE_CUDA(ctx, dcoef.alloc((size_t)(ni + 1) * nfits));
     ATE_CUDA(ctx, dstd.alloc(sd_len * nfits));
     ATE_CUDA(ctx, dsti.alloc(si_len * nfits));
     ATE_CUDA(ctx, dout.alloc(out_len * nfits));
-    ATE_CUDA(ctx, ddone.alloc(nfits));
+    ATE_CUDA(ctx, ddone.alloc(3 * (size_t)nfits));
     ATE_CUDA(ctx, dfits.alloc(nfits));
     ATE_CUDA(ctx, cudaMemsetAsync(dout.p, 0, sizeof(double) * out_len * nfits, ctx->stream));
-    ATE_CUDA(ctx, cudaMemsetAsync(ddone.p, 0, sizeof(int) * nfits, ctx->stream));
+    ATE_CUDA(ctx, cudaMemsetAsync(ddone.p, 0, sizeof(int) * 3 * nfits, ctx->stream));
     const int ev_blocks = ctx->num_sms * 2;
     ATE_CUDA(ctx, dpart.alloc((size_t)ev_blocks * (plen > nlam ? plen : nlam)));
     if (vp_host) {
@@ -733,13 +802,12 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         LognetFit &g = hf[id];
         g.list = probs[p].d_list;
         g.nt = fit_nt[id]; g.hole_begin = fit_hb[id]; g.hole_len = fit_hl[id];
-        g.ni = ni; g.iy = iy;
+        g.ni = ni; g.iy = iy; g.ldh = ldh;
         g.owned = (id < nlead || po.shard_count <= 1 || ((id - nlead) % po.shard_count) == po.shard_rank) ? 1 : 0;
         g.vp = vp_host ? dvp.p : nullptr;
         g.nlam = nlam; g.thr = po.thr; g.maxit = po.maxit;
         g.v = dvr.p + vr_off[id];
-        g.r = g.v + fit_nt[id];
-        g.H = dH.p + n2 * id;
+        g.H = dH.p + h2 * id;
         g.sums = dsums.p + (size_t)plen * id;
         g.coef = dcoef.p + (size_t)(ni + 1) * id;
         g.st_d = dstd.p + sd_len * id;
@@ -753,13 +821,14 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         } else {
             g.flmin = 1.0;
             g.ulam = hf[p].alm;
-            g.nlam_ptr = hf[p].st_i + 4 * (size_t)ni + SI_LMU;
+            g.nlam_ptr = hf[p].st_i + si_scal + SI_LMU;
         }
     }
     ATE_CUDA(ctx, cudaMemcpyAsync(dfits.p, hf.data(), sizeof(LognetFit) * nfits, cudaMemcpyHostToDevice, ctx->stream));
 
     const size_t ev_smem = sizeof(double) * (size_t)(EV_THREADS / 32) * plen;
-    const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * 4 * (size_t)ni;
+    const size_t pre_smem = sizeof(double) * ((size_t)ni + 32);
+    const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * (4 * (size_t)ni + ldh);
     if (ev_smem > 200 * 1024 || cd_smem > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
     int rc = dispatch_iter(ni, [&](auto it) {
         constexpr int IT = decltype(it)::value;
@@ -769,17 +838,18 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     });
     if (rc < 0) return ate_fail(ctx, -1, "cv_binomial: cannot size eval kernel");
     if (cd_smem > 48 * 1024)
-        ATE_CUDA(ctx, cudaFuncSetAttribute(lognet_cd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cd_smem));
+        ATE_CUDA(ctx, cudaFuncSetAttribute(lognet_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cd_smem));
 
     lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits.p, X, ld);
     ATE_LAUNCHED(ctx);
 
-    std::vector<int> hdone(nfits, 0);
+    std::vector<int> hdone(nfits, 0), hflags(3 * (size_t)nfits, 0);
     for (int id = 0; id < nfits; ++id)
         if (!hf[id].owned) hdone[id] = 1;
     int rounds = 0;
     const int max_rounds = nlam * 60 + 100;
-    // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds
+    // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds.
+    // One round = evaluation pass -> bookkeeping -> Gram over the strong set -> CD solve.
     for (int phase = 0; phase < 2; ++phase) {
         const int lo = phase == 0 ? 0 : nlead, hi = phase == 0 ? nlead : nfits;
         if (lo == hi) continue;
@@ -788,23 +858,36 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             for (int id = lo; id < hi; ++id) {
                 if (hdone[id]) continue;
                 ++live;
-                int rc2 = dispatch_iter(ni, [&](auto it) {
+                dispatch_iter(ni, [&](auto it) {
                     constexpr int IT = decltype(it)::value;
                     lognet_eval_kernel<IT><<<ev_blocks, EV_THREADS, ev_smem, ctx->stream>>>(dfits.p, id, X, ld, dpart.p);
                     return 0;
                 });
-                (void)rc2;
                 ATE_LAUNCHED(ctx);
-                fold_partials_kernel<<<(plen + 255) / 256, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, plen, hf[id].sums);
+                fold_partials_kernel<<<(plen + 7) / 8, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, plen, hf[id].sums);
                 ATE_LAUNCHED(ctx);
-                ATE_TRY(ate_i_gram(ctx, X, ld, ni, hf[id].list, 0, hf[id].nt, hf[id].v, hf[id].H,
-                                   hf[id].hole_begin, hf[id].hole_len));
             }
             if (!live) break;
-            lognet_cd_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits.p + lo, ddone.p + lo);
+            lognet_pre_kernel<<<hi - lo, CD_THREADS, pre_smem, ctx->stream>>>(dfits.p + lo, ddone.p + 3 * (size_t)lo);
             ATE_LAUNCHED(ctx);
-            ATE_CUDA(ctx, cudaMemcpyAsync(hdone.data() + lo, ddone.p + lo, sizeof(int) * (hi - lo), cudaMemcpyDeviceToHost, ctx->stream));
+            ATE_CUDA(ctx, cudaMemcpyAsync(hflags.data() + 3 * (size_t)lo, ddone.p + 3 * (size_t)lo,
+                                          sizeof(int) * 3 * (hi - lo), cudaMemcpyDeviceToHost, ctx->stream));
             ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            int solving = 0;
+            for (int id = lo; id < hi; ++id) {
+                if (hdone[id]) continue;
+                hdone[id] = hflags[3 * (size_t)id];
+                const int nS = hflags[3 * (size_t)id + 1];
+                if (!hflags[3 * (size_t)id + 2]) continue;
+                ++solving;
+                if (nS > 0)
+                    ATE_TRY(ate_i_gram(ctx, X, ld, nS, hf[id].list, 0, hf[id].nt, hf[id].v, hf[id].H,
+                                       hf[id].hole_begin, hf[id].hole_len, hf[id].st_i + 5 * (size_t)ni, ldh, ldh));
+            }
+            if (solving) {
+                lognet_solve_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits.p + lo);
+                ATE_LAUNCHED(ctx);
+            }
             if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
         }
     }
@@ -836,7 +919,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
                 return 0;
             });
             ATE_LAUNCHED(ctx);
-            fold_partials_kernel<<<(nlam + 255) / 256, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, nlam, dcv.p + (size_t)q * nlam);
+            fold_partials_kernel<<<(nlam + 7) / 8, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, nlam, dcv.p + (size_t)q * nlam);
             ATE_LAUNCHED(ctx);
         }
         hcv.resize((size_t)nfol * nlam);
@@ -854,7 +937,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         for (int id = 0; id < nfits; ++id) {
             if (!hf[id].owned) continue;
             const double *dv = hsd.data() + sd_len * (size_t)id + 7 * (size_t)ni;
-            const int *iv = hsi.data() + si_len * (size_t)id + 4 * (size_t)ni;
+            const int *iv = hsi.data() + si_len * (size_t)id + si_scal;
             stats->solves += iv[SI_ROUNDS];
             stats->sum_strong += dv[SD_SUMS];
             stats->sum_strong2 += dv[SD_SUMS2];
@@ -865,7 +948,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     for (int q = 0; q < nfol; ++q) {
         const int id = nlead + q;
         if (!hf[id].owned) continue;
-        const int *fv = hsi.data() + si_len * (size_t)id + 4 * (size_t)ni;
+        const int *fv = hsi.data() + si_len * (size_t)id + si_scal;
         fstat[3 * q] = fv[SI_LMU];
         fstat[3 * q + 1] = fv[SI_NLP];
         fstat[3 * q + 2] = fv[SI_JERR];
@@ -883,7 +966,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     outs.assign(P, CvOut());
     for (int p = 0; p < P; ++p) {
         CvOut &o = outs[p];
-        const int *iv = hsi.data() + si_len * (size_t)p + 4 * (size_t)ni;
+        const int *iv = hsi.data() + si_len * (size_t)p + si_scal;
         const double *dv = hsd.data() + sd_len * (size_t)p + 7 * (size_t)ni;
         o.lmu = iv[SI_LMU];
         o.nlp = iv[SI_NLP];

@@ -1,0 +1,75 @@
+# ate_functions_b200.R -- replacement bodies for the hot-path closures of ate_functions.R.
+# Same names, same formals (new ones appended with defaults), same return values.
+# NOT RUN IN THIS IMAGE (no R).  Source after ate_functions.R:  source("ate_functions_b200.R")
+.ate_ctx <- NULL
+ate_ctx <- function(device = 0L) {
+  if (is.null(.ate_ctx)) .ate_ctx <<- .Call("C_ate_ctx_create", as.integer(device))
+  .ate_ctx
+}
+
+.cv_glmnet_b200 <- function(x, y, family = 0L, penalty.factor = NULL, nfolds = 10L, foldid = NULL) {
+  # cv.glmnet draws foldid = sample(rep(seq(nfolds), length = N)) from R's RNG; do it here so the
+  # global stream advances exactly as with glmnet, then hand the ids down (validation mode)
+  if (is.null(foldid)) foldid <- sample(rep(seq(nfolds), length = nrow(x)))
+  .Call("C_ate_cv_glmnet", ate_ctx(), as.integer(family), x, as.double(y), penalty.factor,
+        as.integer(max(foldid)), as.integer(foldid), 0L)
+}
+
+# ate_functions.R:89-108
+ate_condmean_lasso <- function(dataset, treatment_var, outcome_var) {
+  regs <- c(covariates, treatment_var)
+  x <- as.matrix(dataset[regs]); y <- as.matrix(dataset[, outcome_var])
+  pfac <- c(rep(1, length(covariates)), 0)
+  model <- .cv_glmnet_b200(x, y, 0L, pfac)
+  betaw <- model$beta[length(regs), model$idx.1se]          # coef(model)[treatment_var, ], s = "lambda.1se"
+  data.frame(Method = "Single-equation LASSO", ATE = betaw, lower_ci = betaw, upper_ci = betaw)
+}
+
+# ate_functions.R:111-130
+ate_lasso <- function(dataset, treatment_var, outcome_var) {
+  regs <- c(covariates, treatment_var)
+  x <- as.matrix(dataset[regs]); y <- as.matrix(dataset[, outcome_var])
+  model <- .cv_glmnet_b200(x, y, 0L, rep(1, length(regs)))
+  betaw <- model$beta[length(regs), model$idx.1se]
+  data.frame(Method = "Usual LASSO", ATE = betaw, lower_ci = betaw, upper_ci = betaw)
+}
+
+# ate_functions.R:133-146
+prop_score_lasso <- function(dataset, treatment_var) {
+  x <- as.matrix(dataset[covariates]); w <- as.matrix(dataset[, treatment_var])
+  model <- .cv_glmnet_b200(x, w, 1L)
+  s <- model$idx.1se
+  .Call("C_ate_predict", ate_ctx(), x, model$a0[s], model$beta[, s], TRUE)   # n x 1 matrix
+}
+
+# ate_functions.R:267-283
+tau_hat_dr_est <- function(w, y, p, tauhat0x, tauhat1x) {
+  bootstrap_sample_idx <- sample(length(w), length(w), replace = T)
+  .Call("C_ate_tau_hat_dr_est", ate_ctx(), as.double(w), as.double(y), as.double(p),
+        as.double(tauhat0x), as.double(tauhat1x), as.integer(bootstrap_sample_idx))
+}
+
+# ate_functions.R:241-263 (the tail of doubly_robust / doubly_robust_glm; nuisances as today)
+.dr_tail <- function(w, y, p, tauhat0x, tauhat1x, bootstrap_se, method, B = 1000, boot_idx = NULL) {
+  ts <- .Call("C_ate_aipw_score", ate_ctx(), as.double(w), as.double(y), as.double(p),
+              as.double(tauhat0x), as.double(tauhat1x))
+  tau_hat <- ts[1]
+  se_hat <- if (bootstrap_se == T) {
+    attr(.Call("C_ate_bootstrap", ate_ctx(), as.double(w), as.double(y), as.double(p), as.double(tauhat0x),
+               as.double(tauhat1x), as.integer(B), boot_idx, 1991), "sd")
+  } else ts[2]
+  data.frame(Method = method, ATE = tau_hat, lower_ci = tau_hat - se_hat * 1.96, upper_ci = tau_hat + se_hat * 1.96)
+}
+
+# the composite of SURVEY.md section 8 (new; the reference's only sample-splitting precedent is :372-389)
+crossfit_aipw <- function(dataset, treatment_var, outcome_var, bootstrap_se = T, B = 1000, K = 5,
+                          seed = 1991, foldid = NULL, inner_ps = NULL, inner_out = NULL, boot_idx = NULL,
+                          expand = 0L, n_continuous = 0L) {
+  x <- as.matrix(dataset[covariates])
+  r <- .Call("C_ate_crossfit_aipw", ate_ctx(), x, as.double(dataset[, treatment_var]),
+             as.double(dataset[, outcome_var]), as.integer(K), as.integer(if (bootstrap_se) B else 0L),
+             as.integer(seed), foldid, inner_ps, inner_out, boot_idx, as.integer(expand), as.integer(n_continuous))
+  se <- if (bootstrap_se) r[3] else r[2]
+  data.frame(Method = "Cross-fitted AIPW with glmnet nuisances", ATE = r[1],
+             lower_ci = r[1] - 1.96 * se, upper_ci = r[1] + 1.96 * se)
+}
