@@ -70,6 +70,7 @@ SIGNATURES = {
                                 C.POINTER(C.c_int), _vp, C.POINTER(C.c_int)]),
     "ate_predict": (C.c_int, [_vp, c_ll, C.c_int, _vp, C.c_double, _vp, C.c_int, _vp]),
     "ate_aipw_score": (C.c_int, [_vp, c_ll, _vp, _vp, _vp, _vp, _vp, c_dp, c_dp, _vp, _vp, C.c_int]),
+    "ate_aipw_score_static": (C.c_int, [_vp, c_ll, _vp, _vp, _vp, _vp, _vp, c_dp, c_dp]),
     "ate_bootstrap": (C.c_int, [_vp, c_ll, _vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, _vp,
                                 C.c_uint64, c_ll, _vp, c_dp, C.c_int]),
     "ate_tau_hat_dr_est": (C.c_int, [_vp, c_ll, _vp, _vp, _vp, _vp, _vp, _vp, c_dp]),

@@ -122,6 +122,24 @@ ATE_API int ate_aipw_score(ate_ctx *ctx, long long n, const double *w, const dou
                    const double *m0, const double *m1, double *tau, double *se, double *est1,
                    double *est2, int on_device);
 
+/* ---- the same score without any device allocation --------------------------------------- */
+/* No counterpart in the reference.  For callers that cannot call cudaMalloc: code running inside
+ * a memory pool that already owns the whole GPU, or on a latency-critical path where the device
+ * synchronisation hidden in cudaMalloc/cudaFree is not acceptable.  ate_aipw_score() keeps its
+ * per-block partial sums in scratch that the ctx grows with cudaMalloc; this variant keeps them in
+ * a fixed 48 KB array inside the library (resident on every GPU that loads it, until exit) and
+ * calls no allocating routine.  All five inputs are DEVICE pointers of length n; tau and se are
+ * host outputs.  Limits and rules:
+ *   - n <= 2^28 (268,435,456) rows; larger n is refused with an error, nothing is launched;
+ *   - every call on a device shares the one array and finds the previous call's contents in it
+ *     (the entry point clears what must start at zero); calls that overlap on the same GPU race
+ *     and must be serialised by the caller;
+ *   - the first call on each device resolves the array's device address: make that first call
+ *     before any stream capture begins. */
+ATE_API int ate_aipw_score_static(ate_ctx *ctx, long long n, const double *d_w, const double *d_y,
+                                  const double *d_p, const double *d_m0, const double *d_m1,
+                                  double *tau, double *se);
+
 /* ---- a9/a10: bootstrap SE with nuisances held fixed  (ate_functions.R:245-252,267-283) - */
 /* mode ATE_BOOT_INDEX: idx[B*n] (replicate-major, 1-based) is R's sample(n, n, replace = T)
  * per replicate.  mode ATE_BOOT_PHILOX: indices are drawn on device; replicate b uses the
