@@ -26,6 +26,7 @@ struct ate_ctx {
     // profiling of the dominant kernel (weighted Gram)
     bool profile = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    std::vector<std::pair<int, long long>> prof_shape;  // (columns in the Gram, rows) per timed launch
     double prof_flops = 0.0, prof_bytes = 0.0;
     long long prof_launches = 0;
     // small reusable device scratch (block partials, flags)
@@ -130,6 +131,8 @@ int ate_i_standardize(ate_ctx *ctx, double *d_x, long long n, int p, const int *
                       double *d_center, double *d_scale);
 int ate_i_build_design(ate_ctx *ctx, const double *d_xbase, long long n, int p0, int expand,
                        const double *d_w, const double *d_y, double *d_X, long long ld);
+int ate_i_gather_rows(ate_ctx *ctx, const double *X, long long ld, const int32_t *list, long long nt,
+                      int ncs, double *Xp, long long ldp);
 int ate_i_fill_column(ate_ctx *ctx, double *X, long long n, long long ld, int col, double value);
 int ate_i_score(ate_ctx *ctx, long long n, const double *w, const double *y, const double *p,
                 const double *m0, const double *m1, double *d_est1, double *d_est2,

@@ -1,6 +1,7 @@
 // ctx.cu -- context, error plumbing, scratch pools and the host-side R-compatible RNG (f1).
 #include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -82,6 +83,7 @@ extern "C" int ate_profile_enable(ate_ctx *ctx, int on) {
         cudaEventDestroy(pr.second);
     }
     ctx->prof_events.clear();
+    ctx->prof_shape.clear();
     ctx->prof_flops = ctx->prof_bytes = 0.0;
     ctx->prof_launches = 0;
     ctx->profile = on != 0;
@@ -93,11 +95,20 @@ extern "C" int ate_profile_read(ate_ctx *ctx, double *gram_ms, long long *gram_l
     if (!ctx) return -1;
     ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     double ms = 0.0;
+    // ATE_PROFILE_CSV=<file>: one line per timed launch (columns in the Gram, rows, ms)
+    const char *csv = getenv("ATE_PROFILE_CSV");
+    FILE *fp = csv ? fopen(csv, "w") : nullptr;
+    if (fp) fprintf(fp, "launch,gram_cols,rows,ms\n");
+    size_t k = 0;
     for (auto &pr : ctx->prof_events) {
         float t = 0.f;
         ATE_CUDA(ctx, cudaEventElapsedTime(&t, pr.first, pr.second));
         ms += t;
+        if (fp && k < ctx->prof_shape.size())
+            fprintf(fp, "%zu,%d,%lld,%.6f\n", k, ctx->prof_shape[k].first, ctx->prof_shape[k].second, (double)t);
+        ++k;
     }
+    if (fp) fclose(fp);
     if (gram_ms) *gram_ms = ms;
     if (gram_launches) *gram_launches = ctx->prof_launches;
     if (gram_flops) *gram_flops = ctx->prof_flops;

@@ -175,6 +175,21 @@ __global__ void transpose_kernel(const double *__restrict__ x, long long n, int 
     }
 }
 
+// private, contiguous copy of a row subset: Xp[t][0..ncs) = X[list[t]][0..ncs), pad columns zero.
+// One warp per row, 16-byte accesses.
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const double *__restrict__ X, long long ld, const int32_t *__restrict__ list,
+                   long long nt, int ncs, double *__restrict__ Xp, long long ldp) {
+    const int lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const long long wstride = (long long)gridDim.x * nw;
+    for (long long t = (long long)blockIdx.x * nw + (threadIdx.x >> 5); t < nt; t += wstride) {
+        const long long r = list ? (long long)__ldg(list + t) : t;
+        const double2 *src = reinterpret_cast<const double2 *>(X + (size_t)r * (size_t)ld);
+        double2 *dst = reinterpret_cast<double2 *>(Xp + (size_t)t * (size_t)ldp);
+        for (int c = lane; c < (int)(ldp / 2); c += 32) dst[c] = (2 * c < ncs) ? __ldg(src + c) : make_double2(0.0, 0.0);
+    }
+}
+
 __global__ void fill_column_kernel(double *__restrict__ X, long long n, long long ld, int col,
                                    double value) {
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -222,6 +237,17 @@ int ate_i_transpose_to_rowmajor(ate_ctx *ctx, const double *x_colmajor, long lon
                                 double *X, long long ld, int col_offset) {
     dim3 grid((unsigned)((n + 31) / 32), (unsigned)((p + 31) / 32));
     transpose_kernel<<<grid, dim3(32, 8), 0, ctx->stream>>>(x_colmajor, n, p, X, ld, col_offset);
+    ATE_LAUNCHED(ctx);
+    return 0;
+}
+
+int ate_i_gather_rows(ate_ctx *ctx, const double *X, long long ld, const int32_t *list, long long nt,
+                      int ncs, double *Xp, long long ldp) {
+    if (nt <= 0) return 0;
+    if (ncs % 2 != 0 || ldp % 2 != 0 || ldp < ncs || ncs > ld) return ate_fail(ctx, -1, "gather_rows: bad widths");
+    int blocks = ctx->num_sms * 8;
+    if ((nt + 7) / 8 < blocks) blocks = (int)((nt + 7) / 8);
+    gather_rows_kernel<<<blocks, 256, 0, ctx->stream>>>(X, ld, list, nt, ncs, Xp, ldp);
     ATE_LAUNCHED(ctx);
     return 0;
 }

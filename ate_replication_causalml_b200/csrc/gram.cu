@@ -24,6 +24,7 @@
 // Algorithmic work per launch: nrows * p * (p + 1) flop (lower triangle incl.
 // diagonal), nrows * (p + 1) * 8 bytes.
 #include "common.cuh"
+#include "irls_step.cuh"
 
 namespace {
 
@@ -153,6 +154,7 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
         const bool active = q < nblk;
         int bi = 0, bj = 0;
         if (active) block_coords(q, bi, bj);
+        const bool diag = (bi == bj);
         double acc[4][4][2];
 #pragma unroll
         for (int a = 0; a < 4; ++a)
@@ -188,7 +190,9 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
 #pragma unroll
                     for (int m = 0; m < 4; ++m)
 #pragma unroll
-                        for (int nn = 0; nn < 4; ++nn) dmma884(acc[m][nn][0], acc[m][nn][1], a[m], b[nn]);
+                        for (int nn = 0; nn < 4; ++nn)
+                            if (!diag || nn <= m)  // a diagonal block only needs its lower 8x8 tiles
+                                dmma884(acc[m][nn][0], acc[m][nn][1], a[m], b[nn]);
                 }
             }
             __syncwarp();
@@ -238,6 +242,12 @@ gram_fold_kernel(const double *__restrict__ partials, int nchunks, int nblk, int
 }
 
 }  // namespace
+
+int ate_i_gram_fold(ate_ctx *ctx, const double *partials, int nchunks, int nblk, int p, int ldg, double *G) {
+    gram_fold_kernel<<<nblk, 256, 0, ctx->stream>>>(partials, nchunks, nblk, p, ldg, G);
+    ATE_LAUNCHED(ctx);
+    return 0;
+}
 
 // X: row-major device design (ld doubles per row; columns [0, round_up(p,32)) must be readable
 // and zero beyond the real columns).  rows: device row list or NULL.  v: device weights indexed
@@ -297,6 +307,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
     if (ctx->profile) {
         ATE_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
         ctx->prof_events.emplace_back(e0, e1);
+        ctx->prof_shape.emplace_back(-p, nrows);
         ctx->prof_launches++;
         ctx->prof_flops += (double)nrows * p * (p + 1.0);
         ctx->prof_bytes += (double)nrows * (ncols + 1.0) * 8.0;  // whole staged rows + the weight

@@ -4,40 +4,43 @@
 // glmnet's lognet2n touches the n observations in three places per IRLS step: the curvature
 // xv_j = sum v x_j^2, the coordinate gradients g_k = <r, x_k> inside the coordinate-descent
 // sweeps (O(n) each), and the refresh of (q, v, r).  Here every O(n) piece of one IRLS step
-// is done by two passes:
-//   lognet_eval_kernel : eta = a0 + x beta, q = plogis(eta) (glmnet's clamping), v = w q (1-q),
-//                        r = w (y - q); plus sum v, sum r, deviance, X^T r and X^T v.
-//                        One warp per observation row, rows read once (HBM-bound).
-//   gram.cu            : H = X^T V X on the DMMA pipe (tensor-bound, the dominant cost).
-// and the coordinate descent then runs on the p x p quadratic:
+// is ONE pass over the rows (irls_step.cu): eta, q (glmnet's clamping), v, r, sum v, sum r,
+// deviance, X^T r, X^T v, and H = X_L^T V X_L on the DMMA pipe over a column list L that
+// covers the strong set.  The coordinate descent then runs on the p x p quadratic:
 //   lognet_pre_kernel  : one CTA per fit: convergence test of the previous quadratic, KKT check,
 //                        recording / advancing lambda, strong-rule update.  Only the strong
 //                        set's columns enter the Gram (on average ~1/6 of p at C1, i.e. ~4 % of
-//                        the flops), so this runs BEFORE the Gram pass and hands it the list.
+//                        the flops).  If a column joined that the fused step's list missed
+//                        (rare: the list carries a 10 % margin), a plain Gram over the exact
+//                        list runs before the solve.
 //   lognet_solve_kernel: one CTA per fit.  Standardises the compact H in place (lstandard1's
 //                        centring and 1/N scaling are affine in H, X^T v, sum v), then follows
 //                        lognet2n's loop order exactly -- strong-set sweep, intercept step,
 //                        active-set loop -- with g_k = <r, x_k> kept current by covariance
 //                        updates g -= d * H[:,k].  In exact arithmetic the iterates equal glmnet's.
 // All fits of a batch (the full-data fits of every outer fold, then all their CV folds) advance
-// one IRLS step per round; finished fits drop out.  The host reads one small flag vector per
-// round.
+// one IRLS step per round; finished fits drop out.  The host reads two small flag vectors per
+// round (after the bookkeeping: who is done / needs a Gram; after the solve: next list lengths).
 #include <math.h>
+#include <stdlib.h>
 
+#include "irls_step.cuh"
 #include "path.cuh"
 
 namespace {
 
 enum { PH_INIT = 0, PH_REFRESH = 1 };
 enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_SUMS, SD_SUMS2, SD_SUMA, SD_N };
-enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_N };
+enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_NG, SI_HMAP, SI_MISS, SI_N };
 // sums layout: gr[ni] = X^T r, hx[ni] = X^T v, hxx[ni] = sum v x^2, then XMZ, SR, DEV
 enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
 
 struct LognetFit {
+    const double *X;      // the design this fit reads: the shared one (with a row list) or a
+    long long ld;         //   private contiguous copy of its rows (list == NULL)
     const int32_t *list;  // row ids (NULL = identity)
     long long nt, hole_begin, hole_len;
-    int ni, iy, owned, ldh;
+    int ni, iy, owned, ldh, ncs;  // ncs: columns staged per row by the fused step = its zero slot
     const double *vp;
     double flmin;
     const double *ulam;
@@ -50,7 +53,7 @@ struct LognetFit {
     double *sums;     // 3 ni + SU_N
     double *coef;     // ni + 1 (a0 last): raw-scale coefficients for the next eval
     double *st_d;     // b, bs, xv, ga, xm, xs, vq [7 ni] + SD_N
-    int *st_i;        // ixx, mm, mlist, ju, spos [5 ni] + slist [ldh] + SI_N
+    int *st_i;        // ixx, mm, mlist, ju, spos, gpos [6 ni] + slist [ldh] + glist [ldh] + SI_N
     double *alm, *a0, *dev, *beta;  // outputs
 };
 
@@ -60,112 +63,10 @@ constexpr int CD_THREADS = 256;
 __device__ __forceinline__ long long phys_pos(const LognetFit &f, long long t) {
     return t + (t >= f.hole_begin ? f.hole_len : 0);
 }
-__device__ __forceinline__ int *fit_slist(const LognetFit &f) { return f.st_i + 5 * (size_t)f.ni; }
-__device__ __forceinline__ int *fit_scal_i(const LognetFit &f) { return f.st_i + 5 * (size_t)f.ni + f.ldh; }
+__device__ __forceinline__ int *fit_slist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni; }
+__device__ __forceinline__ int *fit_glist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + f.ldh; }
+__device__ __forceinline__ int *fit_scal_i(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + 2 * (size_t)f.ldh; }
 __device__ __forceinline__ double *fit_scal_d(const LognetFit &f) { return f.st_d + 7 * (size_t)f.ni; }
-
-// ---- per-row pass -------------------------------------------------------------------------
-// One warp per observation; the next row's loads are issued before the current row is reduced so
-// that two rows (4 KB at p = 256) are in flight per warp.
-template <int ITER>
-__global__ void __launch_bounds__(EV_THREADS)
-lognet_eval_kernel(const LognetFit *__restrict__ fits, int fid, const double *__restrict__ X,
-                   long long ld, double *__restrict__ partials) {
-    const LognetFit f = fits[fid];
-    extern __shared__ double sm[];  // [warps][3*ni + SU_N]
-    const int ni = f.ni;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const int plen = 3 * ni + SU_N;
-    double beta[2 * ITER], gr[2 * ITER], hx[2 * ITER], hxx[2 * ITER];
-#pragma unroll
-    for (int i = 0; i < ITER; ++i) {
-        const int c = 2 * lane + 64 * i;
-        beta[2 * i] = c < ni ? f.coef[c] : 0.0;
-        beta[2 * i + 1] = c + 1 < ni ? f.coef[c + 1] : 0.0;
-        gr[2 * i] = gr[2 * i + 1] = hx[2 * i] = hx[2 * i + 1] = hxx[2 * i] = hxx[2 * i + 1] = 0.0;
-    }
-    const double a0 = f.coef[ni];
-    const double w = 1.0 / (double)f.nt;
-    const double pmin = GLM_PMIN, fmax_ = log(1.0 / pmin - 1.0), fmin_ = -fmax_;
-    double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0;
-    const long long wstride = (long long)gridDim.x * nw;
-    long long t = (long long)blockIdx.x * nw + wid;
-    double xn[2 * ITER];
-    double yn = 0.0;
-    auto load_row = [&](long long tt) {
-        const long long pp = phys_pos(f, tt);
-        const long long row = f.list ? (long long)__ldg(f.list + pp) : pp;
-        const double *xr = X + (size_t)row * (size_t)ld;
-#pragma unroll
-        for (int i = 0; i < ITER; ++i) {
-            const int c = 2 * lane + 64 * i;
-            double2 t2 = make_double2(0.0, 0.0);
-            if (c + 1 < ld) t2 = __ldg(reinterpret_cast<const double2 *>(xr + c));
-            xn[2 * i] = t2.x;
-            xn[2 * i + 1] = t2.y;
-        }
-        yn = __ldg(xr + f.iy);
-    };
-    if (t < f.nt) load_row(t);
-    for (; t < f.nt; t += wstride) {
-        double x[2 * ITER];
-        double dot = 0.0;
-#pragma unroll
-        for (int i = 0; i < 2 * ITER; ++i) {
-            x[i] = xn[i];
-            dot += x[i] * beta[i];
-        }
-        const double yi = yn;
-        if (t + wstride < f.nt) load_row(t + wstride);
-        const double fi = a0 + warp_sum(dot);
-        double q;
-        if (fi < fmin_)
-            q = 0.0;
-        else if (fi > fmax_)
-            q = 1.0;
-        else
-            q = 1.0 / (1.0 + exp(-fi));
-        const double vi = w * q * (1.0 - q), ri = w * (yi - q);
-        if (lane == 0) {
-            f.v[t] = vi;
-            const double qc = fmin(fmax(q, pmin), 1.0 - pmin);
-            s_xmz += vi;
-            s_sr += ri;
-            s_dev -= w * (yi * log(qc) + (1.0 - yi) * log(1.0 - qc));
-        }
-#pragma unroll
-        for (int i = 0; i < 2 * ITER; ++i) {
-            const double vx = vi * x[i];
-            gr[i] += ri * x[i];
-            hx[i] += vx;
-            hxx[i] += vx * x[i];
-        }
-    }
-    double *mine = sm + (size_t)wid * plen;
-#pragma unroll
-    for (int i = 0; i < ITER; ++i) {
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const int c = 2 * lane + 64 * i + h;
-            if (c < ni) {
-                mine[c] = gr[2 * i + h];
-                mine[ni + c] = hx[2 * i + h];
-                mine[2 * ni + c] = hxx[2 * i + h];
-            }
-        }
-    }
-    if (lane == 0) {
-        mine[3 * ni + SU_XMZ] = s_xmz;
-        mine[3 * ni + SU_SR] = s_sr;
-        mine[3 * ni + SU_DEV] = s_dev;
-    }
-    __syncthreads();
-    for (int e = threadIdx.x; e < plen; e += blockDim.x) {
-        double s = 0.0;
-        for (int q = 0; q < nw; ++q) s += sm[(size_t)q * plen + e];
-        partials[(size_t)blockIdx.x * plen + e] = s;
-    }
-}
 
 // one warp per output element, partials folded in a fixed (lane-strided, then butterfly) order
 __global__ void __launch_bounds__(256)
@@ -181,8 +82,10 @@ fold_partials_kernel(const double *__restrict__ partials, int nparts, int len, d
 
 // sum of the response column over the fit's rows -> q0, bz; arms the first eval
 __global__ void __launch_bounds__(256)
-lognet_init_kernel(const LognetFit *__restrict__ fits, const double *__restrict__ X, long long ld) {
+lognet_init_kernel(const LognetFit *__restrict__ fits) {
     const LognetFit f = fits[blockIdx.x];
+    const double *X = f.X;
+    const long long ld = f.ld;
     __shared__ double red[32];
     double acc[1] = {0.0};
     for (long long t = threadIdx.x; t < f.nt; t += blockDim.x) {
@@ -242,7 +145,9 @@ __device__ __forceinline__ double bmax_all(double v, double *red) {
 // ---- IRLS round, part 1: bookkeeping that needs only the evaluation pass --------------------
 // Convergence of the previous quadratic, KKT re-check, recording lambda, advancing it, and the
 // strong-set update.  Leaves the (padded) strong-column list for the Gram pass and tells the host
-// how many columns it holds.  flags_out[3*fit + {0,1,2}] = {done, nS, solve pending}.
+// how many columns it holds.  flags_out[4*fit + {0,1,2,3}] = {done, nS, solve pending, Gram missing}:
+// the fused step computed H over last round's prediction of the strong set; when a column joined
+// that the prediction missed, the host runs a plain Gram over the exact list before the solve.
 __global__ void __launch_bounds__(CD_THREADS)
 lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_out) {
     const LognetFit f = fits[blockIdx.x];
@@ -251,9 +156,10 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
     double *sd = fit_scal_d(f);
     if (si[SI_DONE]) {
         if (tid == 0) {
-            flags_out[3 * blockIdx.x] = 1;
-            flags_out[3 * blockIdx.x + 1] = 0;
-            flags_out[3 * blockIdx.x + 2] = 0;
+            flags_out[4 * blockIdx.x] = 1;
+            flags_out[4 * blockIdx.x + 1] = 0;
+            flags_out[4 * blockIdx.x + 2] = 0;
+            flags_out[4 * blockIdx.x + 3] = 0;
             si[SI_SOLVE] = 0;
         }
         return;
@@ -262,7 +168,7 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
     double *g = sm, *red = g + ni;  // red[32]
     double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gga = Gxv + ni, *Gxm = Gga + ni,
            *Gxs = Gxm + ni, *Gvq = Gxs + ni;
-    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni;
+    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni, *Ggpos = Gspos + ni;
     int *slist = fit_slist(f);
     const double *gr = f.sums, *hx = f.sums + ni, *hxx = f.sums + 2 * ni;
     const double xmz = f.sums[3 * ni + SU_XMZ], sr_in = f.sums[3 * ni + SU_SR];
@@ -299,8 +205,12 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
             Gmm[j] = 0;
             Gml[j] = 0;
             Gspos[j] = -1;
+            Ggpos[j] = -1;
         }
-        for (int c = tid; c < f.ldh; c += T) slist[c] = f.ldh;  // sentinel: the Gram kernel's zero slot
+        for (int c = tid; c < f.ldh; c += T) {
+            slist[c] = f.ncs;  // sentinel: the staged rows' zero slot
+            fit_glist(f)[c] = f.ncs;
+        }
         vs = bsum_all(vs, red);
         for (int j = tid; j < ni; j += T) Gvq[j] = Gvq[j] * (double)ni / vs;
         __syncthreads();
@@ -405,12 +315,16 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
     __syncthreads();
     if (tid == 0) {
         // newly strong columns join the Gram's column list in ascending order (deterministic)
+        int miss = 0;
         for (int k = 0; k < ni; ++k)
             if (Gixx[k] == 2) {
                 Gixx[k] = 1;
                 Gspos[k] = nS;
                 slist[nS++] = k;
+                if (Ggpos[k] < 0) miss = 1;  // not in the list the fused step built H over
             }
+        si[SI_HMAP] = miss;                   // 1: the host recomputes H over slist -> positions = spos
+        si[SI_MISS] += miss;
         sd[SD_AL] = al;
         sd[SD_AL0] = al0;
         sd[SD_DEV0] = dev0;
@@ -427,32 +341,43 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
             // sequence is handed to the CV folds
             if (f.flmin < 1.0 && si[SI_LMU] > 2) f.alm[0] = exp(2.0 * log(f.alm[1]) - log(f.alm[2]));
         }
-        flags_out[3 * blockIdx.x] = finished ? 1 : 0;
-        flags_out[3 * blockIdx.x + 1] = nS;
-        flags_out[3 * blockIdx.x + 2] = finished ? 0 : 1;
+        flags_out[4 * blockIdx.x] = finished ? 1 : 0;
+        flags_out[4 * blockIdx.x + 1] = nS;
+        flags_out[4 * blockIdx.x + 2] = finished ? 0 : 1;
+        flags_out[4 * blockIdx.x + 3] = (!finished && miss && nS > 0) ? 1 : 0;
     }
 }
 
 // ---- IRLS round, part 2: solve the penalised quadratic on the strong set -------------------
+// H holds X_L^T V X_L over a column list L: the list the fused step used (positions gpos) or, after
+// a missed prediction, the exact strong list (positions spos).  At the end the list for the next
+// fused step is rebuilt: the strong set plus every column whose gradient is within 10 % of the
+// next strong-rule / KKT threshold.  ng_out[fit] = its length.
 __global__ void __launch_bounds__(CD_THREADS)
-lognet_solve_kernel(const LognetFit *__restrict__ fits) {
+lognet_solve_kernel(const LognetFit *__restrict__ fits, int *__restrict__ ng_out) {
     const LognetFit f = fits[blockIdx.x];
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x, ldh = f.ldh;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
-    if (si[SI_DONE] || !si[SI_SOLVE]) return;
+    if (si[SI_DONE] || !si[SI_SOLVE]) {
+        if (tid == 0) ng_out[blockIdx.x] = si[SI_DONE] ? 0 : si[SI_NG];
+        return;
+    }
     extern __shared__ double sm[];
     double *b = sm, *g = b + ni, *hxs = g + ni, *xv = hxs + ni, *vq = xv + ni, *red = vq + ni;  // red[32]
-    int *ixx = reinterpret_cast<int *>(red + 32), *mm = ixx + ni, *ml = mm + ni, *spos = ml + ni,
-        *sl = spos + ni;
+    int *ixx = reinterpret_cast<int *>(red + 32), *mm = ixx + ni, *ml = mm + ni, *hp = ml + ni,
+        *sl = hp + ni;
     double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gxm = Gxv + 2 * ni, *Gxs = Gxm + ni,
            *Gvq = Gxs + ni;
-    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni;
+    int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni,
+        *Ggpos = Gspos + ni;
     const int *slist = fit_slist(f);
+    int *glist = fit_glist(f);
     double *H = f.H;
-    const double *gr = f.sums, *hx = f.sums + ni, *hxx = f.sums + 2 * ni;
+    const double *gr = f.sums, *hx = f.sums + ni;
     const double xmz = f.sums[3 * ni + SU_XMZ], sr_in = f.sums[3 * ni + SU_SR];
     const int nS = si[SI_NS], ilm = si[SI_ILM];
+    const int *hmap = si[SI_HMAP] ? Gspos : Ggpos;
     int nin = si[SI_NIN], nlp = si[SI_NLP];
     double b0 = sd[SD_B0];
     const double al1 = sd[SD_AL], shr = sd[SD_SHR];
@@ -465,32 +390,32 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits) {
         ixx[j] = Gixx[j];
         mm[j] = Gmm[j];
         ml[j] = Gml[j];
-        spos[j] = Gspos[j];
+        hp[j] = hmap[j];
         g[j] = ok ? (gr[j] - m * sr_in) / s : 0.0;
         hxs[j] = ok ? (hx[j] - m * xmz) / s : 0.0;
-        // curvature of the standardised column: sum v (x - m)^2 / s^2
-        const double xvj = ok ? (hxx[j] - 2.0 * m * hx[j] + m * m * xmz) / (s * s) : 0.0;
-        xv[j] = xvj;
+        xv[j] = 0.0;
         Gbs[j] = b[j];
-        Gxv[j] = xvj;
     }
     for (int c = tid; c < nS; c += T) sl[c] = slist[c];
     __syncthreads();
-    // standardise the compact Gram in place: lstandard1's centring and scaling are affine in it
+    // standardise the strong block of H in place: lstandard1's centring and scaling are affine in it
     for (int e = tid; e < nS * nS; e += T) {
         const int a = e / nS, c = e - a * nS;
         const int ja = sl[a], jc = sl[c];
         const double ma = Gxm[ja], mc = Gxm[jc];
-        double *h = H + (size_t)a * ldh + c;
-        *h = (*h - ma * hx[jc] - mc * hx[ja] + ma * mc * xmz) / (Gxs[ja] * Gxs[jc]);
-    }
-    {   // statistics: size of the strong set (what the column-restricted Gram had to cover)
-        if (tid == 0) {
-            sd[SD_SUMS] += (double)nS;
-            sd[SD_SUMS2] += (double)nS * nS;
-            sd[SD_SUMA] += (double)nin;
-            sd[SD_BS0] = b0;
+        double *h = H + (size_t)hp[ja] * ldh + hp[jc];
+        const double t = (*h - ma * hx[jc] - mc * hx[ja] + ma * mc * xmz) / (Gxs[ja] * Gxs[jc]);
+        *h = t;
+        if (a == c) {  // the curvature xv_j = sum v x_j^2 of the standardised column
+            xv[ja] = t;
+            Gxv[ja] = t;
         }
+    }
+    if (tid == 0) {
+        sd[SD_SUMS] += (double)nS;
+        sd[SD_SUMS2] += (double)nS * nS;
+        sd[SD_SUMA] += (double)nin;
+        sd[SD_BS0] = b0;
     }
     __syncthreads();
     double sr = sr_in;
@@ -517,8 +442,11 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits) {
                     ml[nin - 1] = k;
                 }
             }
-            const double *hk = H + (size_t)spos[k] * ldh;
-            for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hk[c];
+            const double *hk = H + (size_t)hp[k] * ldh;
+            for (int c = tid; c < nS; c += T) {
+                const int jj = sl[c];
+                g[jj] -= d * hk[hp[jj]];
+            }
             __syncthreads();
         }
         {
@@ -551,8 +479,11 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits) {
                 sr -= d * hxs[k];
                 __syncthreads();
                 if (tid == 0) b[k] = bn;
-                const double *hk = H + (size_t)spos[k] * ldh;
-                for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hk[c];
+                const double *hk = H + (size_t)hp[k] * ldh;
+                for (int c = tid; c < nS; c += T) {
+                    const int jj = sl[c];
+                    g[jj] -= d * hk[hp[jj]];
+                }
                 __syncthreads();
             }
             const double d = sr / xmz;
@@ -583,7 +514,43 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits) {
         Gml[j] = ml[j];
     }
     const double dotbm = bsum_all(part, red);
+    // ---- column list of the next fused step: the strong set, then the likely joiners.  g[] of a
+    //      non-strong column is still the gradient this round started from. ----
+    double tnext;
+    {
+        const int nlam = (f.flmin < 1.0) ? f.nlam : min(f.nlam, *f.nlam_ptr);
+        const double alf = sd[SD_ALF];
+        double aln;
+        if (f.flmin >= 1.0)
+            aln = (ilm + 1 < nlam) ? f.ulam[ilm + 1] : al1;
+        else if (ilm == 0) {
+            double t = 0.0;
+            for (int j = tid; j < ni; j += T)
+                if (Gju[j] && vq[j] > 0.0) t = fmax(t, fabs(g[j]) / vq[j]);
+            aln = alf * bmax_all(t, red);
+        } else
+            aln = al1 * alf;
+        const double cur = (ilm == 0 && f.flmin < 1.0) ? aln / alf : al1;  // lambda_1 = "big" has no meaning here
+        tnext = 0.9 * fmin(2.0 * aln - cur, cur);
+        if (!(tnext > 0.0)) tnext = 0.0;
+    }
+    for (int j = tid; j < ni; j += T) Ggpos[j] = -1;
+    __syncthreads();
     if (tid == 0) {
+        int nG = 0;
+        for (int c = 0; c < nS; ++c) {
+            glist[nG] = sl[c];
+            Ggpos[sl[c]] = nG++;
+        }
+        for (int k = 0; k < ni && nG < ldh; ++k)
+            if (!ixx[k] && Gju[k] && fabs(g[k]) > tnext * vq[k]) {
+                glist[nG] = k;
+                Ggpos[k] = nG++;
+            }
+        const int npad = (nG + 31) / 32 * 32;
+        for (int c = nG; c < npad && c < ldh; ++c) glist[c] = f.ncs;
+        si[SI_NG] = nG;
+        ng_out[blockIdx.x] = nG;
         f.coef[ni] = b0 - dotbm;
         sd[SD_B0] = b0;
         si[SI_NIN] = nin;
@@ -600,9 +567,11 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits) {
 // rows = the fit's hole (its held-out inner fold).  grid.y = chunks of LC lambdas.
 template <int ITER>
 __global__ void __launch_bounds__(256)
-lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, const double *__restrict__ X,
-                    long long ld, int LC, double *__restrict__ partials /*[gridDim.x][nlam]*/) {
+lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, int LC,
+                    double *__restrict__ partials /*[gridDim.x][nlam]*/) {
     const LognetFit f = fits[fid];
+    const double *X = f.X;
+    const long long ld = f.ld;
     extern __shared__ double sm[];  // beta chunk [LC][ni] + a0[LC] + red [warps][LC]
     const int ni = f.ni;
     const int lmu = fit_scal_i(f)[SI_LMU];
@@ -765,10 +734,12 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     }
     const int plen = 3 * ni + SU_N;
     const int ldh = (ni + 31) / 32 * 32;
-    if (ldh > ld) return ate_fail(ctx, -1, "cv_binomial: design ld (%lld) < padded feature count (%d)", ld, ldh);
+    // the fused step stages [0, ncs) of every row: the features and the response column
+    const int ncs = ((ni > iy ? ni : iy) + 1 + 7) / 8 * 8;
+    if (ldh > ld || ncs > ld) return ate_fail(ctx, -1, "cv_binomial: design ld (%lld) too small for %d features", ld, ni);
     const size_t h2 = (size_t)ldh * ldh;
-    const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 5 * (size_t)ni + ldh + SI_N;
-    const size_t si_scal = 5 * (size_t)ni + ldh;
+    const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 6 * (size_t)ni + 2 * (size_t)ldh + SI_N;
+    const size_t si_scal = 6 * (size_t)ni + 2 * (size_t)ldh;
     const size_t out_len = 3 * (size_t)nlam + (size_t)ni * nlam;
     DevBuf<double> dvr, dH, dsums, dcoef, dstd, dout, dvp, dulam, dpart;
     DevBuf<int> dsti, ddone, dnl;
@@ -780,10 +751,10 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     ATE_CUDA(ctx, dstd.alloc(sd_len * nfits));
     ATE_CUDA(ctx, dsti.alloc(si_len * nfits));
     ATE_CUDA(ctx, dout.alloc(out_len * nfits));
-    ATE_CUDA(ctx, ddone.alloc(3 * (size_t)nfits));
+    ATE_CUDA(ctx, ddone.alloc(5 * (size_t)nfits));
     ATE_CUDA(ctx, dfits.alloc(nfits));
     ATE_CUDA(ctx, cudaMemsetAsync(dout.p, 0, sizeof(double) * out_len * nfits, ctx->stream));
-    ATE_CUDA(ctx, cudaMemsetAsync(ddone.p, 0, sizeof(int) * 3 * nfits, ctx->stream));
+    ATE_CUDA(ctx, cudaMemsetAsync(ddone.p, 0, sizeof(int) * 5 * nfits, ctx->stream));
     const int ev_blocks = ctx->num_sms * 2;
     ATE_CUDA(ctx, dpart.alloc((size_t)ev_blocks * (plen > nlam ? plen : nlam)));
     if (vp_host) {
@@ -796,13 +767,37 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         ATE_CUDA(ctx, dnl.alloc(1));
         ATE_CUDA(ctx, cudaMemcpyAsync(dnl.p, &nlam, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     }
+    // Private contiguous copy of every problem's rows (in list order, pitch = staged width + 4):
+    // the fused step then stages a whole slot with one bulk copy instead of one per row, which
+    // is what lets it reach HBM speed.  ~100 passes per fit amortise the one gather.  Falls back
+    // to the shared design + row lists when the copies would not fit comfortably.
+    const long long ldp = ncs + 4;
+    std::vector<double *> Xp(P, nullptr);
+    DevBuf<double> dXp;
+    {
+        size_t need = 0, free_b = 0, total_b = 0;
+        for (int p = 0; p < P; ++p) need += (size_t)probs[p].nt * (size_t)ldp;
+        ATE_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
+        const char *off = getenv("ATE_NO_PRIVATE_COPY");
+        if (!(off && off[0] == '1') && need * sizeof(double) < free_b / 2) {
+            ATE_CUDA(ctx, dXp.alloc(need));
+            size_t o = 0;
+            for (int p = 0; p < P; ++p) {
+                Xp[p] = dXp.p + o;
+                ATE_TRY(ate_i_gather_rows(ctx, X, ld, probs[p].d_list, probs[p].nt, ncs, Xp[p], ldp));
+                o += (size_t)probs[p].nt * (size_t)ldp;
+            }
+        }
+    }
     std::vector<LognetFit> hf(nfits);
     for (int id = 0; id < nfits; ++id) {
         const int p = id < nlead ? id : (id - nlead) / F;
         LognetFit &g = hf[id];
-        g.list = probs[p].d_list;
+        g.X = Xp[p] ? Xp[p] : X;
+        g.ld = Xp[p] ? ldp : ld;
+        g.list = Xp[p] ? nullptr : probs[p].d_list;
         g.nt = fit_nt[id]; g.hole_begin = fit_hb[id]; g.hole_len = fit_hl[id];
-        g.ni = ni; g.iy = iy; g.ldh = ldh;
+        g.ni = ni; g.iy = iy; g.ldh = ldh; g.ncs = ncs;
         g.owned = (id < nlead || po.shard_count <= 1 || ((id - nlead) % po.shard_count) == po.shard_rank) ? 1 : 0;
         g.vp = vp_host ? dvp.p : nullptr;
         g.nlam = nlam; g.thr = po.thr; g.maxit = po.maxit;
@@ -826,30 +821,26 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     }
     ATE_CUDA(ctx, cudaMemcpyAsync(dfits.p, hf.data(), sizeof(LognetFit) * nfits, cudaMemcpyHostToDevice, ctx->stream));
 
-    const size_t ev_smem = sizeof(double) * (size_t)(EV_THREADS / 32) * plen;
     const size_t pre_smem = sizeof(double) * ((size_t)ni + 32);
     const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * (4 * (size_t)ni + ldh);
-    if (ev_smem > 200 * 1024 || cd_smem > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
-    int rc = dispatch_iter(ni, [&](auto it) {
-        constexpr int IT = decltype(it)::value;
-        if (ev_smem > 48 * 1024)
-            if (cudaFuncSetAttribute(lognet_eval_kernel<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ev_smem) != cudaSuccess) return -1;
-        return 0;
-    });
-    if (rc < 0) return ate_fail(ctx, -1, "cv_binomial: cannot size eval kernel");
+    if (cd_smem > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
     if (cd_smem > 48 * 1024)
         ATE_CUDA(ctx, cudaFuncSetAttribute(lognet_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cd_smem));
+    int rc = 0;
 
-    lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits.p, X, ld);
+    lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits.p);
     ATE_LAUNCHED(ctx);
 
-    std::vector<int> hdone(nfits, 0), hflags(3 * (size_t)nfits, 0);
+    std::vector<int> hdone(nfits, 0), hflags(4 * (size_t)nfits, 0), hng(nfits, 0);
+    std::vector<char> started(nfits, 0);
     for (int id = 0; id < nfits; ++id)
         if (!hf[id].owned) hdone[id] = 1;
+    int *dflags = ddone.p, *dng = ddone.p + 4 * (size_t)nfits;
     int rounds = 0;
     const int max_rounds = nlam * 60 + 100;
     // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds.
-    // One round = evaluation pass -> bookkeeping -> Gram over the strong set -> CD solve.
+    // One round = fused IRLS step (evaluation + Gram over the predicted list) -> bookkeeping ->
+    // (rarely) a Gram over the exact strong list -> coordinate-descent solve.
     for (int phase = 0; phase < 2; ++phase) {
         const int lo = phase == 0 ? 0 : nlead, hi = phase == 0 ? nlead : nfits;
         if (lo == hi) continue;
@@ -858,35 +849,41 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             for (int id = lo; id < hi; ++id) {
                 if (hdone[id]) continue;
                 ++live;
-                dispatch_iter(ni, [&](auto it) {
-                    constexpr int IT = decltype(it)::value;
-                    lognet_eval_kernel<IT><<<ev_blocks, EV_THREADS, ev_smem, ctx->stream>>>(dfits.p, id, X, ld, dpart.p);
-                    return 0;
-                });
-                ATE_LAUNCHED(ctx);
-                fold_partials_kernel<<<(plen + 7) / 8, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, plen, hf[id].sums);
-                ATE_LAUNCHED(ctx);
+                IrlsStep st;
+                st.X = hf[id].X; st.ld = hf[id].ld; st.ncols = ncs;
+                st.rows = hf[id].list; st.nrows = hf[id].nt;
+                st.hole_begin = hf[id].hole_begin; st.hole_len = hf[id].hole_len;
+                st.ni = ni; st.iy = iy; st.coef = hf[id].coef; st.w = 1.0 / (double)hf[id].nt;
+                st.colidx = hf[id].st_i + 6 * (size_t)ni + ldh;  // the list the last solve left
+                st.nG = hng[id];
+                st.H = hf[id].H; st.ldh = ldh; st.sums = hf[id].sums; st.v_out = hf[id].v;
+                st.init = started[id] ? 0 : 1;
+                started[id] = 1;
+                ATE_TRY(ate_i_irls_step(ctx, st));
             }
             if (!live) break;
-            lognet_pre_kernel<<<hi - lo, CD_THREADS, pre_smem, ctx->stream>>>(dfits.p + lo, ddone.p + 3 * (size_t)lo);
+            lognet_pre_kernel<<<hi - lo, CD_THREADS, pre_smem, ctx->stream>>>(dfits.p + lo, dflags + 4 * (size_t)lo);
             ATE_LAUNCHED(ctx);
-            ATE_CUDA(ctx, cudaMemcpyAsync(hflags.data() + 3 * (size_t)lo, ddone.p + 3 * (size_t)lo,
-                                          sizeof(int) * 3 * (hi - lo), cudaMemcpyDeviceToHost, ctx->stream));
+            ATE_CUDA(ctx, cudaMemcpyAsync(hflags.data() + 4 * (size_t)lo, dflags + 4 * (size_t)lo,
+                                          sizeof(int) * 4 * (hi - lo), cudaMemcpyDeviceToHost, ctx->stream));
             ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
             int solving = 0;
             for (int id = lo; id < hi; ++id) {
                 if (hdone[id]) continue;
-                hdone[id] = hflags[3 * (size_t)id];
-                const int nS = hflags[3 * (size_t)id + 1];
-                if (!hflags[3 * (size_t)id + 2]) continue;
+                hdone[id] = hflags[4 * (size_t)id];
+                const int nS = hflags[4 * (size_t)id + 1];
+                if (!hflags[4 * (size_t)id + 2]) continue;
                 ++solving;
-                if (nS > 0)
-                    ATE_TRY(ate_i_gram(ctx, X, ld, nS, hf[id].list, 0, hf[id].nt, hf[id].v, hf[id].H,
-                                       hf[id].hole_begin, hf[id].hole_len, hf[id].st_i + 5 * (size_t)ni, ldh, ldh));
+                if (hflags[4 * (size_t)id + 3])  // a column joined that the fused step's list missed
+                    ATE_TRY(ate_i_gram(ctx, hf[id].X, hf[id].ld, nS, hf[id].list, 0, hf[id].nt, hf[id].v, hf[id].H,
+                                       hf[id].hole_begin, hf[id].hole_len, hf[id].st_i + 6 * (size_t)ni, ncs, ldh));
             }
             if (solving) {
-                lognet_solve_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits.p + lo);
+                lognet_solve_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits.p + lo, dng + lo);
                 ATE_LAUNCHED(ctx);
+                ATE_CUDA(ctx, cudaMemcpyAsync(hng.data() + lo, dng + lo, sizeof(int) * (hi - lo),
+                                              cudaMemcpyDeviceToHost, ctx->stream));
+                ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
             }
             if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
         }
@@ -915,7 +912,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             ATE_CUDA(ctx, cudaMemsetAsync(dpart.p, 0, sizeof(double) * (size_t)ev_blocks * nlam, ctx->stream));
             dispatch_iter(ni, [&](auto it) {
                 constexpr int IT = decltype(it)::value;
-                lognet_cvdev_kernel<IT><<<dim3(ev_blocks, nchunk), 256, cv_smem, ctx->stream>>>(dfits.p, id, X, ld, LC, dpart.p);
+                lognet_cvdev_kernel<IT><<<dim3(ev_blocks, nchunk), 256, cv_smem, ctx->stream>>>(dfits.p, id, LC, dpart.p);
                 return 0;
             });
             ATE_LAUNCHED(ctx);

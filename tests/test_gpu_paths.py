@@ -138,6 +138,22 @@ def test_ragged_and_unequal_folds(engine, oracle):
     assert np.allclose(g["cvm"], o["cvm"], rtol=1e-10) and g["idx_min"] == o["idx_min"]
 
 
+def test_row_list_mode_equals_private_copy_mode(engine, oracle, monkeypatch):
+    """The binomial path normally gathers each problem's rows into a private contiguous copy (one
+    bulk copy per slot); when memory is short it reads the shared design through row lists.  Both
+    must give the same fit."""
+    d = _data(2500, 7)
+    xs = _scaled(oracle, d)
+    fid = synth.fold_ids(2500, 10, 5)
+    a = engine.cv_glmnet(xs, d["w"], "binomial", foldid=fid)
+    monkeypatch.setenv("ATE_NO_PRIVATE_COPY", "1")
+    b = engine.cv_glmnet(xs, d["w"], "binomial", foldid=fid)
+    assert a["lmu"] == b["lmu"] and a["idx_1se"] == b["idx_1se"]
+    assert np.abs(a["beta"] - b["beta"]).max() < 1e-10 and np.allclose(a["cvm"], b["cvm"], rtol=1e-10)
+    o = oracle.cv_glmnet(xs, d["w"], fid, "binomial")
+    assert np.abs(b["beta"] - o["beta"]).max() < 1e-9
+
+
 def test_predict_link_and_response(engine, oracle):
     d = _data(4001, 7)
     beta = np.r_[0.3, 0, -0.2, 0, 0, 1.5, 0]
