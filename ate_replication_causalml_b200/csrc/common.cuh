@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <map>
 #include <string>
 #include <vector>
 
@@ -36,6 +37,8 @@ struct ate_ctx {
     void *gram_scratch = nullptr;
     size_t gram_scratch_bytes = 0;
     ate_rng_state rng;
+    // large work buffers kept across calls (cudaMalloc/cudaFree of multi-GB blocks cost ~1 s per fit)
+    std::map<std::string, std::pair<void *, size_t>> cache;
     // multi-GPU: host-buffer sum over the ranks that share one fit
     ate_allreduce_fn allreduce = nullptr;
     void *allreduce_user = nullptr;
@@ -89,6 +92,8 @@ struct DevBuf {
 };
 
 int ate_scratch(ate_ctx *ctx, size_t bytes, void **out);
+// persistent, grow-only buffer identified by `tag`; released by ate_ctx_destroy
+int ate_cached(ate_ctx *ctx, const char *tag, size_t bytes, void **out);
 int ate_gram_scratch(ate_ctx *ctx, size_t bytes, void **out);
 
 // ---- device helpers ---------------------------------------------------------------------

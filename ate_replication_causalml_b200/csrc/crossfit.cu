@@ -255,8 +255,12 @@ extern "C" int ate_crossfit_aipw(ate_ctx *ctx, const ate_crossfit_opts *opts, lo
     }
     const int p = o.expand == 0 ? p0 : (o.expand == 1 ? p0 * p0 : p0 + p0 * p0);
     const long long ld = round_up(p + 3, 32);
-    DevBuf<double> dX;
-    ATE_CUDA(ctx, dX.alloc(N * (size_t)ld));
+    struct { double *p; } dX;
+    {
+        void *pool = nullptr;
+        ATE_TRY(ate_cached(ctx, "crossfit.design", sizeof(double) * N * (size_t)ld, &pool));
+        dX.p = (double *)pool;
+    }
     ATE_TRY(ate_i_build_design(ctx, dbase.p, n, p0, o.expand, dwy.p, dwy.p + N, dX.p, ld));
     ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     dbase.release();

@@ -54,6 +54,8 @@ extern "C" void ate_ctx_destroy(ate_ctx *ctx) {
         cudaEventDestroy(pr.first);
         cudaEventDestroy(pr.second);
     }
+    for (auto &kv : ctx->cache)
+        if (kv.second.first) cudaFree(kv.second.first);
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->gram_scratch) cudaFree(ctx->gram_scratch);
     cudaStreamDestroy(ctx->stream);
@@ -128,6 +130,11 @@ static int grow(ate_ctx *ctx, void **buf, size_t *have, size_t want, void **out)
     }
     *out = *buf;
     return 0;
+}
+
+int ate_cached(ate_ctx *ctx, const char *tag, size_t bytes, void **out) {
+    auto &slot = ctx->cache[tag];
+    return grow(ctx, &slot.first, &slot.second, bytes, out);
 }
 
 int ate_scratch(ate_ctx *ctx, size_t bytes, void **out) {

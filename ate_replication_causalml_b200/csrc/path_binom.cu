@@ -24,6 +24,8 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <chrono>
+
 #include "irls_step.cuh"
 #include "path.cuh"
 
@@ -741,10 +743,15 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 6 * (size_t)ni + 2 * (size_t)ldh + SI_N;
     const size_t si_scal = 6 * (size_t)ni + 2 * (size_t)ldh;
     const size_t out_len = 3 * (size_t)nlam + (size_t)ni * nlam;
-    DevBuf<double> dvr, dH, dsums, dcoef, dstd, dout, dvp, dulam, dpart;
+    double *dvr_p = nullptr;
+    DevBuf<double> dH, dsums, dcoef, dstd, dout, dvp, dulam, dpart;
     DevBuf<int> dsti, ddone, dnl;
     DevBuf<LognetFit> dfits;
-    ATE_CUDA(ctx, dvr.alloc(vr_total));
+    {
+        void *pool = nullptr;
+        ATE_TRY(ate_cached(ctx, "binom.v", vr_total * sizeof(double), &pool));
+        dvr_p = (double *)pool;
+    }
     ATE_CUDA(ctx, dH.alloc(h2 * nfits));
     ATE_CUDA(ctx, dsums.alloc((size_t)plen * nfits));
     ATE_CUDA(ctx, dcoef.alloc((size_t)(ni + 1) * nfits));
@@ -773,17 +780,19 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     // to the shared design + row lists when the copies would not fit comfortably.
     const long long ldp = ncs + 4;
     std::vector<double *> Xp(P, nullptr);
-    DevBuf<double> dXp;
     {
         size_t need = 0, free_b = 0, total_b = 0;
         for (int p = 0; p < P; ++p) need += (size_t)probs[p].nt * (size_t)ldp;
         ATE_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
         const char *off = getenv("ATE_NO_PRIVATE_COPY");
-        if (!(off && off[0] == '1') && need * sizeof(double) < free_b / 2) {
-            ATE_CUDA(ctx, dXp.alloc(need));
+        const auto itc = ctx->cache.find("binom.rows");
+        const size_t have = itc == ctx->cache.end() ? 0 : itc->second.second;  // already ours
+        if (!(off && off[0] == '1') && need * sizeof(double) < (free_b + have) / 2) {
+            void *pool = nullptr;
+            ATE_TRY(ate_cached(ctx, "binom.rows", need * sizeof(double), &pool));
             size_t o = 0;
             for (int p = 0; p < P; ++p) {
-                Xp[p] = dXp.p + o;
+                Xp[p] = (double *)pool + o;
                 ATE_TRY(ate_i_gather_rows(ctx, X, ld, probs[p].d_list, probs[p].nt, ncs, Xp[p], ldp));
                 o += (size_t)probs[p].nt * (size_t)ldp;
             }
@@ -801,7 +810,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         g.owned = (id < nlead || po.shard_count <= 1 || ((id - nlead) % po.shard_count) == po.shard_rank) ? 1 : 0;
         g.vp = vp_host ? dvp.p : nullptr;
         g.nlam = nlam; g.thr = po.thr; g.maxit = po.maxit;
-        g.v = dvr.p + vr_off[id];
+        g.v = dvr_p + vr_off[id];
         g.H = dH.p + h2 * id;
         g.sums = dsums.p + (size_t)plen * id;
         g.coef = dcoef.p + (size_t)(ni + 1) * id;
@@ -828,8 +837,13 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         ATE_CUDA(ctx, cudaFuncSetAttribute(lognet_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cd_smem));
     int rc = 0;
 
+    const bool timing = getenv("ATE_TIMING") != nullptr;
+    auto tnow = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t_mark = 0.0, t_step = 0.0, t_pre = 0.0, t_gram = 0.0, t_solve = 0.0;
+    if (timing) { cudaStreamSynchronize(ctx->stream); t_mark = tnow(); }
     lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits.p);
     ATE_LAUNCHED(ctx);
+    if (timing) { cudaStreamSynchronize(ctx->stream); fprintf(stderr, "[ate timing] init %.1f ms\n", tnow() - t_mark); }
 
     std::vector<int> hdone(nfits, 0), hflags(4 * (size_t)nfits, 0), hng(nfits, 0);
     std::vector<char> started(nfits, 0);
@@ -846,6 +860,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         if (lo == hi) continue;
         for (;;) {
             int live = 0;
+            if (timing) { cudaStreamSynchronize(ctx->stream); t_mark = tnow(); }
             for (int id = lo; id < hi; ++id) {
                 if (hdone[id]) continue;
                 ++live;
@@ -862,11 +877,13 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
                 ATE_TRY(ate_i_irls_step(ctx, st));
             }
             if (!live) break;
+            if (timing) { cudaStreamSynchronize(ctx->stream); const double t = tnow(); t_step += t - t_mark; t_mark = t; }
             lognet_pre_kernel<<<hi - lo, CD_THREADS, pre_smem, ctx->stream>>>(dfits.p + lo, dflags + 4 * (size_t)lo);
             ATE_LAUNCHED(ctx);
             ATE_CUDA(ctx, cudaMemcpyAsync(hflags.data() + 4 * (size_t)lo, dflags + 4 * (size_t)lo,
                                           sizeof(int) * 4 * (hi - lo), cudaMemcpyDeviceToHost, ctx->stream));
             ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if (timing) { const double t = tnow(); t_pre += t - t_mark; t_mark = t; }
             int solving = 0;
             for (int id = lo; id < hi; ++id) {
                 if (hdone[id]) continue;
@@ -878,6 +895,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
                     ATE_TRY(ate_i_gram(ctx, hf[id].X, hf[id].ld, nS, hf[id].list, 0, hf[id].nt, hf[id].v, hf[id].H,
                                        hf[id].hole_begin, hf[id].hole_len, hf[id].st_i + 6 * (size_t)ni, ncs, ldh));
             }
+            if (timing) { cudaStreamSynchronize(ctx->stream); const double t = tnow(); t_gram += t - t_mark; t_mark = t; }
             if (solving) {
                 lognet_solve_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits.p + lo, dng + lo);
                 ATE_LAUNCHED(ctx);
@@ -885,10 +903,16 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
                                               cudaMemcpyDeviceToHost, ctx->stream));
                 ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
             }
+            if (timing) { const double t = tnow(); t_solve += t - t_mark; t_mark = t; }
             if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
         }
     }
 
+    if (timing) {
+        fprintf(stderr, "[ate timing] rounds %d: fused steps %.1f ms, bookkeeping %.1f ms, fallback grams %.1f ms, solves %.1f ms\n",
+                rounds, t_step, t_pre, t_gram, t_solve);
+        t_mark = tnow();
+    }
     // ---- held-out deviance of every CV fold at every lambda ----
     std::vector<double> hcv;
     if (F > 0) {
@@ -922,6 +946,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         hcv.resize((size_t)nfol * nlam);
         ATE_CUDA(ctx, cudaMemcpyAsync(hcv.data(), dcv.p, sizeof(double) * hcv.size(), cudaMemcpyDeviceToHost, ctx->stream));
     }
+    if (timing) { cudaStreamSynchronize(ctx->stream); fprintf(stderr, "[ate timing] cv deviance %.1f ms\n", tnow() - t_mark); }
     std::vector<double> hout(out_len * (size_t)nlead), hsd(sd_len * (size_t)nfits);
     std::vector<int> hsi(si_len * (size_t)nfits);
     ATE_CUDA(ctx, cudaMemcpyAsync(hout.data(), dout.p, sizeof(double) * hout.size(), cudaMemcpyDeviceToHost, ctx->stream));

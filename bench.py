@@ -199,6 +199,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
 
+    import faulthandler
+    faulthandler.dump_traceback_later(1500, exit=True)  # a stuck run leaves a traceback, not silence
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
