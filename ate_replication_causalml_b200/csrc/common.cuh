@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <map>
 #include <string>
@@ -87,7 +88,14 @@ struct DevBuf {
     cudaError_t alloc(size_t count) {
         release();
         n = count;
-        return cudaMalloc((void **)&p, sizeof(T) * (count ? count : 1));
+        cudaError_t e = cudaMalloc((void **)&p, sizeof(T) * (count ? count : 1));
+        // ATE_POISON=1 (debugging): fill fresh buffers with 0xFF (NaN doubles, -1 ints) so that a
+        // read of memory the library never wrote shows up deterministically
+        if (e == cudaSuccess && getenv("ATE_POISON")) {
+            e = cudaMemset(p, 0xFF, sizeof(T) * (count ? count : 1));
+            cudaDeviceSynchronize();  // the ctx stream does not order against the legacy stream
+        }
+        return e;
     }
 };
 

@@ -126,6 +126,10 @@ static int grow(ate_ctx *ctx, void **buf, size_t *have, size_t want, void **out)
         *have = 0;
         size_t cap = want + (want >> 2) + 4096;
         ATE_CUDA(ctx, cudaMalloc(buf, cap));
+        if (getenv("ATE_POISON")) {
+            ATE_CUDA(ctx, cudaMemset(*buf, 0xFF, cap));
+            ATE_CUDA(ctx, cudaDeviceSynchronize());
+        }
         *have = cap;
     }
     *out = *buf;

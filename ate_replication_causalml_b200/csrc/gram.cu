@@ -215,36 +215,35 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
 __global__ void __launch_bounds__(256)
 gram_fold_kernel(const double *__restrict__ partials, int nchunks, int nblk, int p, int ldg,
                  double *__restrict__ G) {
+    // grid = (blocks of the lower triangle, 4): one element per thread, many chunk loads in flight;
+    // the additions stay in chunk order (bit-reproducible)
     const int q = blockIdx.x;
     int bi, bj;
     block_coords(q, bi, bj);
-    // 4 elements per thread, chunk loop unrolled so the loads of several chunks are in flight;
-    // the additions stay in chunk order (bit-reproducible)
-    const int e = threadIdx.x * 4;
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    const int e = blockIdx.y * 256 + threadIdx.x;
     const double *src = partials + (size_t)q * 1024 + e;
     const size_t cstride = (size_t)nblk * 1024;
-#pragma unroll 8
-    for (int c = 0; c < nchunks; ++c) {
-        const double4 t = *reinterpret_cast<const double4 *>(src + (size_t)c * cstride);
-        s0 += t.x; s1 += t.y; s2 += t.z; s3 += t.w;
-    }
-    const double sv[4] = {s0, s1, s2, s3};
-    const int r = bi * 32 + (e >> 5);
+    double s = 0.0;
+    int c = 0;
+    for (; c + 16 <= nchunks; c += 16) {
+        double t[16];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int col = bj * 32 + (e & 31) + k;
-        if (r < p && col < p && col <= r) {
-            G[(size_t)r * ldg + col] = sv[k];
-            G[(size_t)col * ldg + r] = sv[k];
-        }
+        for (int k = 0; k < 16; ++k) t[k] = __ldg(src + (size_t)(c + k) * cstride);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) s += t[k];
+    }
+    for (; c < nchunks; ++c) s += __ldg(src + (size_t)c * cstride);
+    const int r = bi * 32 + (e >> 5), col = bj * 32 + (e & 31);
+    if (r < p && col < p && col <= r) {
+        G[(size_t)r * ldg + col] = s;
+        G[(size_t)col * ldg + r] = s;
     }
 }
 
 }  // namespace
 
 int ate_i_gram_fold(ate_ctx *ctx, const double *partials, int nchunks, int nblk, int p, int ldg, double *G) {
-    gram_fold_kernel<<<nblk, 256, 0, ctx->stream>>>(partials, nchunks, nblk, p, ldg, G);
+    gram_fold_kernel<<<dim3(nblk, 4), 256, 0, ctx->stream>>>(partials, nchunks, nblk, p, ldg, G);
     ATE_LAUNCHED(ctx);
     return 0;
 }
@@ -312,7 +311,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
         ctx->prof_flops += (double)nrows * p * (p + 1.0);
         ctx->prof_bytes += (double)nrows * (ncols + 1.0) * 8.0;  // whole staged rows + the weight
     }
-    gram_fold_kernel<<<nblk, 256, 0, ctx->stream>>>((const double *)scr, nchunks, nblk, p, ldg, G);
+    gram_fold_kernel<<<dim3(nblk, 4), 256, 0, ctx->stream>>>((const double *)scr, nchunks, nblk, p, ldg, G);
     ATE_LAUNCHED(ctx);
     return 0;
 }

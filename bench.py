@@ -200,7 +200,7 @@ def main():
     args = ap.parse_args()
 
     import faulthandler
-    faulthandler.dump_traceback_later(1500, exit=True)  # a stuck run leaves a traceback, not silence
+    faulthandler.dump_traceback_later(int(os.environ.get("ATE_BENCH_WATCHDOG", "1500")), exit=True)  # a stuck run leaves a traceback
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
