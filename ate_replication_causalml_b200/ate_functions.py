@@ -107,6 +107,31 @@ def doubly_robust_scores(w, y, p, tauhat0x, tauhat1x, bootstrap_se=False, B=1000
     return _row(method, tau_hat, tau_hat - se_hat * 1.96, tau_hat + se_hat * 1.96)
 
 
+# ---------------------------------------------------------------- ate_functions.R:211-264
+def doubly_robust_glm(dataset, treatment_var, outcome_var, bootstrap_se=False, B=1000, boot_idx=None,
+                      boot_seed=1991):
+    """The reference function as written: logistic glm for the outcome on all other columns
+    (:218-220), predicted at W := 1 and W := 0 (:221-228), logistic glm propensity on everything but
+    the outcome (:231-234), AIPW (:241-243), sandwich or bootstrap SE (:245-256), interval (:260-263).
+    Every column of `dataset` other than the outcome is a regressor, as `Y ~ .` makes it."""
+    cols = [c for c in dataset.columns if c != outcome_var]
+    xo = dataset[cols].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    w = dataset[treatment_var].to_numpy(dtype=np.float64)
+    condmean = engine().glm_binomial(xo, y)["coef"]
+    jw = cols.index(treatment_var)
+    x1 = xo.copy(); x1[:, jw] = 1.0
+    x0 = xo.copy(); x0[:, jw] = 0.0
+    tauhat1x = engine().predict(x1, condmean[0], condmean[1:], response_binomial=True)
+    tauhat0x = engine().predict(x0, condmean[0], condmean[1:], response_binomial=True)
+    pcols = [c for c in cols if c != treatment_var]
+    xp = dataset[pcols].to_numpy(dtype=np.float64)
+    pcoef = engine().glm_binomial(xp, w)["coef"]
+    p = engine().predict(xp, pcoef[0], pcoef[1:], response_binomial=True)
+    return doubly_robust_scores(w, y, p, tauhat0x, tauhat1x, bootstrap_se=bootstrap_se, B=B, boot_idx=boot_idx,
+                                boot_seed=boot_seed, method="Doubly Robust with logistic regression PS")
+
+
 def crossfit_aipw(dataset, treatment_var, outcome_var, bootstrap_se=True, B=1000, K=5, seed=1991,
                   foldid=None, inner_ps=None, inner_out=None, boot_idx=None, expand=0,
                   n_continuous=0, use_1se=True, method="Cross-fitted AIPW with glmnet nuisances"):

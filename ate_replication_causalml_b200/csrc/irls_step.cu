@@ -62,7 +62,6 @@ struct StepArgs {
     const int *colidx;
     int nblk, stages;
     double *gram_partials, *eval_partials, *v_out;
-    int dbg;  // ATE_STEP_DEBUG bitmask (profiling experiments only): 1 no helper math, 2 no exp, 4 no MMA
 };
 
 template <int ITER, bool INIT>
@@ -231,7 +230,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
             else if (fi > fmax_)
                 q = 1.0;
             else
-                q = (a.dbg & 2) ? 0.5 + 1e-3 * fi : 1.0 / (1.0 + exp(-fi));
+                q = 1.0 / (1.0 + exp(-fi));
             const double vi = w * q * (1.0 - q) * valid, ri = w * (yi - q) * valid;
             __syncwarp();  // every lane has read the validity flag before it is overwritten
             if ((lane & 1) == 0) {
@@ -283,7 +282,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
             mbar_wait(full + s, ph);
-            if (lead && !(a.dbg & 1)) {
+            if (lead) {
                 mbar_wait(vfull + s, ph);
                 const double *base = sx + stage_doubles * s;
 #pragma unroll 4
@@ -351,7 +350,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
             mbar_wait(full + s, ph);
             mbar_wait(vfull + s, ph);
-            if (active && !(a.dbg & 4)) {
+            if (active) {
                 const double *base = sx + stage_doubles * s;
                 const double *vs = sv + s * F_ROWS;
 #pragma unroll
@@ -454,10 +453,6 @@ int ate_i_irls_step(ate_ctx *ctx, const IrlsStep &in) {
     a.gram_partials = (double *)scr;
     a.eval_partials = (double *)scr + gram_doubles;
     a.v_out = in.v_out;
-    {
-        const char *d = getenv("ATE_STEP_DEBUG");
-        a.dbg = d ? atoi(d) : 0;
-    }
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->profile) {
         ATE_CUDA(ctx, cudaEventCreate(&e0));

@@ -162,6 +162,20 @@ class Engine:
                     idx_min=imin.value, idx_1se=i1se.value, dev_ratio=dev[:Lm].copy(),
                     lambda_min=lam[imin.value], lambda_1se=lam[i1se.value])
 
+    def glm_binomial(self, x, y, maxit=25, epsilon=1e-8):
+        """stats::glm(y ~ x, family = binomial): coef = [(Intercept), x...] (ate_functions.R:218-234)."""
+        x = L.fmat(x)
+        y = L.f64(y)
+        n, p = x.shape
+        coef = np.zeros(p + 1)
+        dev = C.c_double()
+        it = C.c_int()
+        conv = C.c_int()
+        self._chk(self._lib.ate_glm_binomial(self._h, n, p, L.ptr(x), L.ptr(y), int(maxit), float(epsilon),
+                                             L.ptr(coef), C.byref(dev), C.byref(it), C.byref(conv)),
+                  "ate_glm_binomial")
+        return dict(coef=coef, deviance=dev.value, iters=it.value, converged=bool(conv.value))
+
     def predict(self, x, a0, beta, response_binomial=False):
         x = L.fmat(x)
         n, p = x.shape

@@ -110,6 +110,14 @@ ATE_API int ate_cv_glmnet(ate_ctx *ctx, int family, long long n, int p, const do
                   double *a0, double *beta, double *cvm, double *cvsd, int *idx_min, int *idx_1se,
                   double *dev_ratio, int *jerr);
 
+/* ---- f2: glm(formula, family = binomial("logit"))  (ate_functions.R:218-220, :231-234) ----- */
+/* The unpenalised logistic nuisance fits of doubly_robust_glm (and :156-158, Rmd:165-168):
+ * glm.fit's IRLS from mustart = (y + 0.5)/2, convergence |dev - devold| / (|dev| + 0.1) < epsilon
+ * (1e-8), at most maxit (25) steps.  x[n*p] has no intercept column; coef[p+1] comes back in R's
+ * order, (Intercept) first.  maxit <= 0 / epsilon <= 0 select glm.control()'s defaults. */
+ATE_API int ate_glm_binomial(ate_ctx *ctx, long long n, int p, const double *x, const double *y, int maxit,
+                             double epsilon, double *coef, double *deviance, int *iters, int *converged);
+
 /* ---- a5: predict(model, newx, type)  (ate_functions.R:144; coef() at :106,:128,:308) --- */
 /* out[n] = a0 + x beta, passed through plogis when response_binomial != 0. */
 ATE_API int ate_predict(ate_ctx *ctx, long long n, int p, const double *x, double a0, const double *beta,

@@ -1207,3 +1207,100 @@ ORC_API int orc_crossfit_aipw(long n, int p, const double *x, const double *w, c
     orc_aipw(n, w, y, phat, m0, m1, tau, se, NULL, NULL);
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------ */
+/* stats::glm(family = binomial("logit")) -- the nuisance fits of doubly_robust_glm      */
+/* (ate_functions.R:218-220, :231-234; also :156-158 and ate_replication.Rmd:165-168)     */
+/* ------------------------------------------------------------------------------------ */
+
+/* binomial()$linkinv as R's C code computes it (family.c: logit_linkinv) */
+static double r_logit_linkinv(double eta) {
+    const double thresh = 30.0, mthresh = -30.0, inveps = 1.0 / 2.220446049250313e-16;
+    double tmp = (eta < mthresh) ? 2.220446049250313e-16 : ((eta > thresh) ? inveps : exp(eta));
+    return tmp / (1.0 + tmp);
+}
+
+static double binom_dev(long n, const double *y, const double *mu) {
+    /* sum(binomial()$dev.resids(y, mu, 1)) with y in {0,1}: y log(y/mu) terms vanish at y = 0 */
+    double s = 0.0;
+    for (long i = 0; i < n; ++i) {
+        double a = y[i] > 0.0 ? y[i] * log(y[i] / mu[i]) : 0.0;
+        double b = y[i] < 1.0 ? (1.0 - y[i]) * log((1.0 - y[i]) / (1.0 - mu[i])) : 0.0;
+        s += 2.0 * (a + b);
+    }
+    return s;
+}
+
+/*
+ * glm.fit's IRLS: mustart = (y + 0.5)/2, weighted least squares each step, stop when
+ * |dev - devold| / (|dev| + 0.1) < epsilon (1e-8), at most maxit (25) steps.
+ * R solves each step by QR (Cdqrls); this restatement solves the same normal equations by a
+ * long-double Cholesky, which agrees to rounding on the well-conditioned designs used here.
+ * x: n*p col-major WITHOUT intercept; coef[p+1]: (Intercept) first, then the columns of x.
+ * Returns 0 if converged, 1 otherwise.
+ */
+ORC_API int orc_glm_binomial(long n, int p, const double *x, const double *y, int maxit,
+                             double epsilon, double *coef, double *deviance, int *iters) {
+    const int q = p + 1;
+    double *eta = (double *)malloc(sizeof(double) * n), *mu = (double *)malloc(sizeof(double) * n);
+    long double *A = (long double *)malloc(sizeof(long double) * q * q);
+    long double *b = (long double *)malloc(sizeof(long double) * q);
+    for (long i = 0; i < n; ++i) {
+        mu[i] = (y[i] + 0.5) / 2.0;
+        eta[i] = log(mu[i] / (1.0 - mu[i]));
+    }
+    double devold = binom_dev(n, y, mu), dev = devold;
+    int conv = 0, it = 0;
+    for (it = 1; it <= maxit; ++it) {
+        for (int a = 0; a < q * q; ++a) A[a] = 0.0L;
+        for (int a = 0; a < q; ++a) b[a] = 0.0L;
+        for (long i = 0; i < n; ++i) {
+            const double w = mu[i] * (1.0 - mu[i]);
+            const double z = eta[i] + (y[i] - mu[i]) / w;
+            /* row (1, x_i) */
+            for (int a = 0; a < q; ++a) {
+                const double xa = a == 0 ? 1.0 : x[(size_t)(a - 1) * n + i];
+                b[a] += (long double)w * xa * z;
+                for (int c = 0; c <= a; ++c) {
+                    const double xc = c == 0 ? 1.0 : x[(size_t)(c - 1) * n + i];
+                    A[a * q + c] += (long double)w * xa * xc;
+                }
+            }
+        }
+        /* Cholesky A = L L^T (lower), solve */
+        for (int a = 0; a < q; ++a) {
+            for (int c = 0; c <= a; ++c) {
+                long double s = A[a * q + c];
+                for (int k = 0; k < c; ++k) s -= A[a * q + k] * A[c * q + k];
+                A[a * q + c] = (a == c) ? sqrtl(s) : s / A[c * q + c];
+            }
+        }
+        for (int a = 0; a < q; ++a) {
+            long double s = b[a];
+            for (int k = 0; k < a; ++k) s -= A[a * q + k] * b[k];
+            b[a] = s / A[a * q + a];
+        }
+        for (int a = q - 1; a >= 0; --a) {
+            long double s = b[a];
+            for (int k = a + 1; k < q; ++k) s -= A[k * q + a] * b[k];
+            b[a] = s / A[a * q + a];
+        }
+        for (int a = 0; a < q; ++a) coef[a] = (double)b[a];
+        for (long i = 0; i < n; ++i) {
+            double e = coef[0];
+            for (int a = 1; a < q; ++a) e += coef[a] * x[(size_t)(a - 1) * n + i];
+            eta[i] = e;
+            mu[i] = r_logit_linkinv(e);
+        }
+        dev = binom_dev(n, y, mu);
+        if (fabs(dev - devold) / (fabs(dev) + 0.1) < epsilon) {
+            conv = 1;
+            break;
+        }
+        devold = dev;
+    }
+    *deviance = dev;
+    *iters = it > maxit ? maxit : it;
+    free(eta); free(mu); free(A); free(b);
+    return conv ? 0 : 1;
+}

@@ -255,3 +255,16 @@ def crossfit_aipw(x, w, y, foldid_, inner_ps, inner_out, nfolds_inner=10, nlambd
                                  _d(m0), _d(m1), C.byref(tau), C.byref(se), _d(lps), _d(lout))
     return dict(rc=rc, phat=phat, m0=m0, m1=m1, tau=tau.value, se=se.value, lambda_ps=lps,
                 lambda_out=lout)
+
+
+def glm_binomial(x, y, maxit=25, epsilon=1e-8):
+    """stats::glm(y ~ x, family = binomial): returns dict(coef[(Intercept), x...], deviance, iters, converged)."""
+    x = _f(x)
+    y = _v(y)
+    n, p = x.shape
+    coef = np.zeros(p + 1)
+    dev = C.c_double(0)
+    it = C.c_int(0)
+    rc = lib().orc_glm_binomial(C.c_long(n), C.c_int(p), _d(x), _d(y), C.c_int(maxit), C.c_double(epsilon),
+                                _d(coef), C.byref(dev), C.byref(it))
+    return dict(coef=coef, deviance=dev.value, iters=it.value, converged=(rc == 0))

@@ -155,6 +155,7 @@ static const R_CallMethodDef call_methods[] = {
     {"C_ate_cv_glmnet", (DL_FUNC)&C_ate_cv_glmnet, 8},
     {"C_ate_predict", (DL_FUNC)&C_ate_predict, 5},
     {"C_ate_aipw_score", (DL_FUNC)&C_ate_aipw_score, 6},
+    {"C_ate_glm_binomial", (DL_FUNC)&C_ate_glm_binomial, 3},
     {"C_ate_bootstrap", (DL_FUNC)&C_ate_bootstrap, 9},
     {"C_ate_tau_hat_dr_est", (DL_FUNC)&C_ate_tau_hat_dr_est, 7},
     {"C_ate_standardize", (DL_FUNC)&C_ate_standardize, 2},

@@ -61,6 +61,21 @@ tau_hat_dr_est <- function(w, y, p, tauhat0x, tauhat1x) {
   data.frame(Method = method, ATE = tau_hat, lower_ci = tau_hat - se_hat * 1.96, upper_ci = tau_hat + se_hat * 1.96)
 }
 
+# ate_functions.R:211-264 -- same formals; only the two glm() calls and the tail change
+doubly_robust_glm <- function(dataset, treatment_var, outcome_var, bootstrap_se = F) {
+  mm <- function(d) model.matrix(~ ., d)[, -1, drop = FALSE]          # what glm builds for `~ .`
+  plogis_lin <- function(x, b) .Call("C_ate_predict", ate_ctx(), x, b[1], b[-1], TRUE)
+  xo <- mm(dataset[, names(dataset) != outcome_var])
+  condmean <- .Call("C_ate_glm_binomial", ate_ctx(), xo, as.double(dataset[, outcome_var]))      # :218-220
+  x1 <- xo; x1[, treatment_var] <- 1; x0 <- xo; x0[, treatment_var] <- 0                       # :221-226
+  tauhat1x <- plogis_lin(x1, condmean); tauhat0x <- plogis_lin(x0, condmean)                   # :227-228
+  xp <- xo[, colnames(xo) != treatment_var, drop = FALSE]
+  pcoef <- .Call("C_ate_glm_binomial", ate_ctx(), xp, as.double(dataset[, treatment_var]))      # :231-233
+  p <- plogis_lin(xp, pcoef)                                                                   # :234
+  .dr_tail(dataset[, treatment_var], dataset[, outcome_var], p, tauhat0x, tauhat1x, bootstrap_se,
+           "Doubly Robust with logistic regression PS")
+}
+
 # the composite of SURVEY.md section 8 (new; the reference's only sample-splitting precedent is :372-389)
 crossfit_aipw <- function(dataset, treatment_var, outcome_var, bootstrap_se = T, B = 1000, K = 5,
                           seed = 1991, foldid = NULL, inner_ps = NULL, inner_out = NULL, boot_idx = NULL,

@@ -172,3 +172,23 @@ def test_expand_order_matches_belloni_loop(oracle):
             cols.append(x[:, c1] * x[:, c2])
     assert (out == np.column_stack(cols)).all()
     assert (oracle.expand_deg2(x, False) == np.column_stack(cols[3:])).all()
+
+
+def test_glm_binomial_is_the_mle_and_matches_glm_fit_conventions(oracle):
+    """stats::glm.fit (ate_functions.R:218-220, 231-234): the fit is the unpenalised MLE (score = 0),
+    stops by |dev - devold| / (|dev| + 0.1) < 1e-8, and agrees with the L1 path's lambda -> 0 end."""
+    rng = np.random.default_rng(11)
+    n, p = 4000, 6
+    x = rng.standard_normal((n, p))
+    y = (rng.random(n) < 1 / (1 + np.exp(-(0.3 + x @ np.array([0.8, -0.5, 0, 0.2, 0, 1.0]))))).astype(float)
+    g = oracle.glm_binomial(x, y)
+    assert g["converged"] and 3 <= g["iters"] <= 8
+    xa = np.column_stack([np.ones(n), x])
+    mu = 1 / (1 + np.exp(-xa @ g["coef"]))
+    assert np.abs(xa.T @ (y - mu)).max() < 1e-6
+    dev = -2 * np.sum(y * np.log(mu) + (1 - y) * np.log1p(-mu))
+    assert abs(dev - g["deviance"]) < 1e-9 * dev
+    path = oracle.glmnet(x, y, "binomial", lambda_=np.array([1e-1, 1e-2, 1e-3, 1e-4, 1e-6, 1e-8]), thresh=1e-12)
+    assert np.abs(path["beta"][:, -1] - g["coef"][1:]).max() < 1e-4
+    # maxit = 1 reports non-convergence, like R's warning
+    assert not oracle.glm_binomial(x, y, maxit=1)["converged"]
