@@ -70,6 +70,8 @@ SIGNATURES = {
                                 C.POINTER(C.c_int), _vp, C.POINTER(C.c_int)]),
     "ate_glm_binomial": (C.c_int, [_vp, c_ll, C.c_int, _vp, _vp, C.c_int, C.c_double, _vp, c_dp,
                                    C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "ate_lm": (C.c_int, [_vp, c_ll, C.c_int, _vp, _vp, _vp, _vp, _vp, c_dp, c_dp, C.POINTER(C.c_int),
+                         C.POINTER(c_ll), _vp]),
     "ate_predict": (C.c_int, [_vp, c_ll, C.c_int, _vp, C.c_double, _vp, C.c_int, _vp]),
     "ate_aipw_score": (C.c_int, [_vp, c_ll, _vp, _vp, _vp, _vp, _vp, c_dp, c_dp, _vp, _vp, C.c_int]),
     "ate_aipw_score_static": (C.c_int, [_vp, c_ll, _vp, _vp, _vp, _vp, _vp, c_dp, c_dp]),

@@ -48,6 +48,61 @@ def _row(method, tau_hat, lower_ci, upper_ci):
                          "upper_ci": [upper_ci]})
 
 
+def _r_mean(x):
+    """base::mean on a double vector: long-double sum / n, then one long-double correction pass
+    (summary.c: real_mean).  The R closure keeps calling mean() itself; this is its host stand-in."""
+    x = np.asarray(x, dtype=np.float64)
+    s = np.sum(x, dtype=np.longdouble) / x.size
+    s += np.sum(x.astype(np.longdouble) - s) / x.size
+    return float(s)
+
+
+def _table_row(method, fit, j):
+    """tau_hat / se_hat from row j of summary(lm)$coefficients, then the +-1.96 interval."""
+    tau_hat, se_hat = float(fit["coef"][j]), float(fit["std_err"][j])
+    if tau_hat != tau_hat:
+        # R: reg_coef["W", "Estimate"] on a table that dropped the aliased row -> subscript out of bounds
+        raise IndexError("subscript out of bounds: the treatment coefficient is aliased (NA)")
+    return _row(method, tau_hat, tau_hat - se_hat * 1.96, tau_hat + se_hat * 1.96)
+
+
+# ---------------------------------------------------------------- ate_functions.R:24-39
+def ate_condmean_ols(dataset, treatment_var, outcome_var, method="Direct Method"):
+    """lm(Y ~ .) on every other column (:25-29); Estimate and Std. Error of the treatment row (:33-34)."""
+    cols = [c for c in dataset.columns if c != outcome_var]
+    fit = engine().lm(dataset[cols].to_numpy(dtype=np.float64), dataset[outcome_var].to_numpy(dtype=np.float64))
+    return _table_row(method, fit, 1 + cols.index(treatment_var))
+
+
+# ---------------------------------------------------------------- ate_functions.R:44-64
+def prop_score_weight(dataset, p, treatment_var, outcome_var, covariates, method="Propensity_Weighting"):
+    """tau_hat_i = (W - p) Y / (p (1 - p)) (:47); its mean is the estimate (:59); the SE comes from the
+    residuals of tau_hat_i regressed on covariates * (W - p) (:50-57).  `covariates` is an ARGUMENT here,
+    as in the reference."""
+    w = dataset[treatment_var].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    p = np.asarray(p, dtype=np.float64).ravel()
+    tau_i = ((w - p) * y) / (p * (1 - p))
+    ps_er = w - p
+    d = dataset[list(covariates)].to_numpy(dtype=np.float64) * ps_er[:, None]
+    fit = engine().lm(d, tau_i)
+    n = w.size
+    se_hat = np.sqrt(fit["rss"] / n) / np.sqrt(n)            # sqrt(mean(e^2)) / sqrt(NROW)
+    tau_hat = _r_mean(tau_i)
+    return _row(method, tau_hat, tau_hat - se_hat * 1.96, tau_hat + se_hat * 1.96)
+
+
+# ---------------------------------------------------------------- ate_functions.R:67-86
+def prop_score_ols(dataset, p, treatment_var, outcome_var, method="Propensity_Regression"):
+    """lm(Y ~ W, weights = W/p + (1 - W)/(1 - p)) (:72-76); treatment row of the table (:80-81)."""
+    w = dataset[treatment_var].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    p = np.asarray(p, dtype=np.float64).ravel()
+    weights = (w / p) + ((1 - w) / (1 - p))
+    fit = engine().lm(w.reshape(-1, 1), y, weights=weights)
+    return _table_row(method, fit, 1)
+
+
 # ---------------------------------------------------------------- ate_functions.R:89-108
 def ate_condmean_lasso(dataset, treatment_var, outcome_var, foldid=None, seed=None):
     regs = list(covariates) + [treatment_var]
@@ -153,7 +208,8 @@ def crossfit_aipw(dataset, treatment_var, outcome_var, bootstrap_se=True, B=1000
 
 
 # ---------------------------------------------------------------- ate_functions.R:286-328
-def belloni_selection(dataset, treatment_var, outcome_var, foldid_xw=None, foldid_xy=None, seed=None):
+def belloni_selection(dataset, treatment_var, outcome_var, foldid_xw=None, foldid_xy=None, seed=None,
+                      return_coefs=False):
     """belloni() up to the post-lasso OLS (which SURVEY.md ranks as the next row, f4): the
     expansion (:288-296), the two gaussian cv.glmnet fits (:304-305), coefficients at
     model_xw$lambda.min for BOTH models (:308-309) and the selected support with the
@@ -171,7 +227,23 @@ def belloni_selection(dataset, treatment_var, outcome_var, foldid_xw=None, foldi
     nz_xy = np.nonzero(c_xy > 0)[0] + 1
     c_union = pd.unique(np.r_[nz_xw, nz_xy]) - 1
     c_union = c_union[c_union > 0]            # x[, 0] is silently dropped by R
+    if return_coefs:
+        return c_union, x, c_xw, c_xy
     return c_union, x
+
+
+def belloni(dataset, treatment_var, outcome_var, method="Belloni et.al", foldid_xw=None, foldid_xy=None, seed=None):
+    """belloni() end to end (:286-328): the double selection above, then lm(y ~ cbind(x[, c_union], w))
+    (:317-320) and the `x_restrictedW` row of its coefficient table (:322-323)."""
+    c_union, x, c_xw, c_xy = belloni_selection(dataset, treatment_var, outcome_var, foldid_xw, foldid_xy, seed,
+                                               return_coefs=True)
+    w = dataset[treatment_var].to_numpy(dtype=np.float64)
+    y = dataset[outcome_var].to_numpy(dtype=np.float64)
+    x_restricted = np.column_stack([x[:, c_union - 1], w])     # R's 1-based x[, c_union]
+    fit = engine().lm(x_restricted, y)
+    out = _table_row(method, fit, x_restricted.shape[1])
+    out.attrs.update(c_union=c_union, c_xw=c_xw, c_xy=c_xy, fit=fit)
+    return out
 
 
 def _coef_at(model, s):

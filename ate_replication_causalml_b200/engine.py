@@ -176,6 +176,26 @@ class Engine:
                   "ate_glm_binomial")
         return dict(coef=coef, deviance=dev.value, iters=it.value, converged=bool(conv.value))
 
+    def lm(self, x, y, weights=None, want_resid=False):
+        """stats::lm(y ~ x[, weights]) + summary(): coef / std_err = [(Intercept), x...], NaN where R says NA
+        (ate_functions.R:25-34, :52-56, :72-81, :320-323)."""
+        x = L.fmat(x)
+        y = L.f64(y)
+        n, p = x.shape
+        w = None if weights is None else L.f64(weights)
+        coef = np.zeros(p + 1)
+        se = np.zeros(p + 1)
+        sigma = C.c_double()
+        rss = C.c_double()
+        rank = C.c_int()
+        df = C.c_longlong()
+        resid = np.empty(n) if want_resid else None
+        self._chk(self._lib.ate_lm(self._h, n, p, L.ptr(x), L.ptr(y), L.ptr(w) if w is not None else None,
+                                   L.ptr(coef), L.ptr(se), C.byref(sigma), C.byref(rss), C.byref(rank),
+                                   C.byref(df), L.ptr(resid) if want_resid else None), "ate_lm")
+        return dict(coef=coef, std_err=se, sigma=sigma.value, rss=rss.value, rank=rank.value,
+                    df_residual=df.value, resid=resid)
+
     def predict(self, x, a0, beta, response_binomial=False):
         x = L.fmat(x)
         n, p = x.shape

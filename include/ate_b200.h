@@ -118,6 +118,20 @@ ATE_API int ate_cv_glmnet(ate_ctx *ctx, int family, long long n, int p, const do
 ATE_API int ate_glm_binomial(ate_ctx *ctx, long long n, int p, const double *x, const double *y, int maxit,
                              double epsilon, double *coef, double *deviance, int *iters, int *converged);
 
+/* ---- f3/f4: lm() + summary(lm)$coefficients  (ate_functions.R:25-34 ate_condmean_ols; :52-56
+ * prop_score_weight's residual regression; :72-81 prop_score_ols, weighted; :320-323 belloni's
+ * post-lasso OLS) ------------------------------------------------------------------------ */
+/* Least squares of y on [1, x] (x: n x p col-major host matrix WITHOUT the intercept column;
+ * weights: n or NULL, as lm(weights=)).  coef / std_err [p+1] in R's order, (Intercept) first; a column
+ * that R's pivoted QR (tol 1e-7) would report as aliased gets NaN in both (R prints NA and
+ * summary() drops the row).  sigma = residual standard error = sqrt(rss / df_residual), rss =
+ * sum w e^2, rank = number of estimable coefficients, df_residual = #(w != 0) - rank.  resid
+ * (optional, host, n): y - fitted (unweighted residuals, residuals(lm)).  Any output but coef may
+ * be NULL.  Returns -1 on bad arguments / negative weights. */
+ATE_API int ate_lm(ate_ctx *ctx, long long n, int p, const double *x, const double *y, const double *weights,
+                   double *coef, double *std_err, double *sigma, double *rss, int *rank,
+                   long long *df_residual, double *resid);
+
 /* ---- a5: predict(model, newx, type)  (ate_functions.R:144; coef() at :106,:128,:308) --- */
 /* out[n] = a0 + x beta, passed through plogis when response_binomial != 0. */
 ATE_API int ate_predict(ate_ctx *ctx, long long n, int p, const double *x, double a0, const double *beta,

@@ -1231,11 +1231,174 @@ static double binom_dev(long n, const double *y, const double *mu) {
     return s;
 }
 
+/* ------------------------------------------------------------------------------------------
+ * Householder QR least squares as R's lm.fit / lm.wfit / glm.fit do it: Cdqrls -> LINPACK dqrdc2
+ * (Householder with LIMITED column pivoting: a column whose remaining norm has fallen below
+ * tol * its original norm is moved to the end and the rank reduced; tol = 1e-7) followed by dqrsl
+ * (Q'y, back-substitution).  [EXT] restated from the published LINPACK/R algorithm; lm call sites:
+ * ate_functions.R:28 (ate_condmean_ols), :53-54 (prop_score_weight), :74-75 (prop_score_ols),
+ * :320 (belloni); glm call sites :218-220, :231-234.
+ * X: n x q col-major, overwritten; y: n, overwritten with Q'y.  pivot[q]: original column of each
+ * position.  coef[q]: by ORIGINAL column, NaN for the aliased ones.  rinv_diag[q] (optional):
+ * diag((X'X)^-1) by original column over the estimable ones (summary.lm's chol2inv(R)).
+ * Returns the rank.
+ */
+static int qr_ls(long n, int q, double *X, double *y, double tol, double *coef, double *xtx_inv_diag) {
+    int *pivot = (int *)malloc(sizeof(int) * q);
+    double *qraux = (double *)malloc(sizeof(double) * q), *w0 = (double *)malloc(sizeof(double) * q),
+           *w1 = (double *)malloc(sizeof(double) * q), *tmpc = (double *)malloc(sizeof(double) * n);
+    for (int j = 0; j < q; ++j) {
+        pivot[j] = j;
+        double s = 0.0;
+        for (long i = 0; i < n; ++i) s += X[(size_t)j * n + i] * X[(size_t)j * n + i];
+        qraux[j] = sqrt(s);
+        w0[j] = qraux[j];
+        w1[j] = qraux[j];
+        if (w1[j] == 0.0) w1[j] = 1.0;
+    }
+    const int lup = q < n ? q : (int)n;
+    int k = q + 1; /* 1-based: rank + 1 */
+    for (int l = 1; l <= lup; ++l) {
+        /* cycle negligible columns to the end */
+        while (l < k && qraux[l - 1] < w1[l - 1] * tol) {
+            const int lp1 = l + 1;
+            memcpy(tmpc, X + (size_t)(l - 1) * n, sizeof(double) * n);
+            const int pi = pivot[l - 1];
+            const double qa = qraux[l - 1], a0 = w0[l - 1], a1 = w1[l - 1];
+            for (int j = lp1; j <= q; ++j) {
+                memcpy(X + (size_t)(j - 2) * n, X + (size_t)(j - 1) * n, sizeof(double) * n);
+                pivot[j - 2] = pivot[j - 1];
+                qraux[j - 2] = qraux[j - 1];
+                w0[j - 2] = w0[j - 1];
+                w1[j - 2] = w1[j - 1];
+            }
+            memcpy(X + (size_t)(q - 1) * n, tmpc, sizeof(double) * n);
+            pivot[q - 1] = pi;
+            qraux[q - 1] = qa;
+            w0[q - 1] = a0;
+            w1[q - 1] = a1;
+            --k;
+        }
+        if (l == n) break;
+        double *xl = X + (size_t)(l - 1) * n;
+        double nrm = 0.0;
+        for (long i = l - 1; i < n; ++i) nrm += xl[i] * xl[i];
+        nrm = sqrt(nrm);
+        if (nrm != 0.0) {
+            if (xl[l - 1] != 0.0) nrm = xl[l - 1] < 0.0 ? -fabs(nrm) : fabs(nrm);
+            for (long i = l - 1; i < n; ++i) xl[i] /= nrm;
+            xl[l - 1] += 1.0;
+            for (int j = l + 1; j <= q; ++j) {
+                double *xj = X + (size_t)(j - 1) * n;
+                double t = 0.0;
+                for (long i = l - 1; i < n; ++i) t -= xl[i] * xj[i];
+                t /= xl[l - 1];
+                for (long i = l - 1; i < n; ++i) xj[i] += t * xl[i];
+                if (qraux[j - 1] != 0.0) {
+                    double tt = 1.0 - (fabs(xj[l - 1]) / qraux[j - 1]) * (fabs(xj[l - 1]) / qraux[j - 1]);
+                    if (tt < 0.0) tt = 0.0;
+                    if (fabs(tt) < 1e-6) {
+                        double s = 0.0;
+                        for (long i = l; i < n; ++i) s += xj[i] * xj[i];
+                        qraux[j - 1] = sqrt(s);
+                        w0[j - 1] = qraux[j - 1];
+                    } else
+                        qraux[j - 1] *= sqrt(tt);
+                }
+            }
+            qraux[l - 1] = xl[l - 1];
+            xl[l - 1] = -nrm;
+        }
+    }
+    int rank = k - 1;
+    if (rank > n) rank = (int)n;
+    /* dqrsl: y <- Q'y over the first `rank` reflectors */
+    for (int l = 1; l <= rank && l < n + 0; ++l) {
+        if (qraux[l - 1] == 0.0) continue;
+        double *xl = X + (size_t)(l - 1) * n;
+        const double save = xl[l - 1];
+        xl[l - 1] = qraux[l - 1];
+        double t = 0.0;
+        for (long i = l - 1; i < n; ++i) t -= xl[i] * y[i];
+        t /= xl[l - 1];
+        for (long i = l - 1; i < n; ++i) y[i] += t * xl[i];
+        xl[l - 1] = save;
+    }
+    for (int j = 0; j < q; ++j) coef[j] = NAN;
+    double *b = (double *)malloc(sizeof(double) * (rank > 0 ? rank : 1));
+    for (int a = rank - 1; a >= 0; --a) {
+        double s = y[a];
+        for (int c = a + 1; c < rank; ++c) s -= X[(size_t)c * n + a] * b[c];
+        b[a] = s / X[(size_t)a * n + a];
+    }
+    for (int a = 0; a < rank; ++a) coef[pivot[a]] = b[a];
+    if (xtx_inv_diag) {
+        /* (R'R)^-1 = R^-1 R^-T; diagonal entry a = sum_c (R^-1)[a,c]^2 over c >= a */
+        double *Ri = (double *)calloc((size_t)(rank > 0 ? rank : 1) * (rank > 0 ? rank : 1), sizeof(double));
+        for (int c = 0; c < rank; ++c) {
+            Ri[(size_t)c * rank + c] = 1.0 / X[(size_t)c * n + c];
+            for (int a = c - 1; a >= 0; --a) {
+                double s = 0.0;
+                for (int m = a + 1; m <= c; ++m) s -= X[(size_t)m * n + a] * Ri[(size_t)c * rank + m];
+                Ri[(size_t)c * rank + a] = s / X[(size_t)a * n + a];
+            }
+        }
+        for (int j = 0; j < q; ++j) xtx_inv_diag[j] = NAN;
+        for (int a = 0; a < rank; ++a) {
+            double s = 0.0;
+            for (int c = a; c < rank; ++c) s += Ri[(size_t)c * rank + a] * Ri[(size_t)c * rank + a];
+            xtx_inv_diag[pivot[a]] = s;
+        }
+        free(Ri);
+    }
+    free(b); free(pivot); free(qraux); free(w0); free(w1); free(tmpc);
+    return rank;
+}
+
+/*
+ * lm(y ~ x [, weights = w]) followed by summary(): lm.fit / lm.wfit (rows scaled by sqrt(w), zero
+ * weights dropped from the degrees of freedom), coefficient table `Estimate`, `Std. Error` =
+ * sqrt(resvar * diag((X'X)^-1)), resvar = rss / rdf, rss = sum w e^2 (summary.lm).
+ * x: n*p col-major WITHOUT intercept; coef/se [p+1], (Intercept) first, NaN = NA (aliased).
+ * resid (optional): y - fitted.  Returns the rank.
+ */
+ORC_API int orc_lm(long n, int p, const double *x, const double *y, const double *w, double *coef,
+                   double *se, double *sigma, double *rss_out, long *rdf_out, double *resid) {
+    const int q = p + 1;
+    double *X = (double *)malloc(sizeof(double) * (size_t)n * q), *yy = (double *)malloc(sizeof(double) * n);
+    double *dinv = (double *)malloc(sizeof(double) * q);
+    long nok = 0;
+    for (long i = 0; i < n; ++i) {
+        const double sw = w ? sqrt(w[i]) : 1.0;
+        if (!w || w[i] != 0.0) ++nok;
+        X[i] = sw;
+        for (int j = 0; j < p; ++j) X[(size_t)(j + 1) * n + i] = sw * x[(size_t)j * n + i];
+        yy[i] = sw * y[i];
+    }
+    const int rank = qr_ls(n, q, X, yy, 1e-7, coef, dinv);
+    double rss = 0.0;
+    for (long i = 0; i < n; ++i) {
+        double f = 0.0;
+        for (int j = 0; j < q; ++j)
+            if (coef[j] == coef[j]) f += coef[j] * (j == 0 ? 1.0 : x[(size_t)(j - 1) * n + i]);
+        const double e = y[i] - f;
+        if (resid) resid[i] = e;
+        rss += (w ? w[i] : 1.0) * e * e;
+    }
+    const long rdf = nok - rank;
+    const double resvar = rdf > 0 ? rss / (double)rdf : NAN;
+    for (int j = 0; j < q; ++j) se[j] = sqrt(resvar * dinv[j]);
+    if (sigma) *sigma = sqrt(resvar);
+    if (rss_out) *rss_out = rss;
+    if (rdf_out) *rdf_out = rdf;
+    free(X); free(yy); free(dinv);
+    return rank;
+}
+
 /*
  * glm.fit's IRLS: mustart = (y + 0.5)/2, weighted least squares each step, stop when
  * |dev - devold| / (|dev| + 0.1) < epsilon (1e-8), at most maxit (25) steps.
- * R solves each step by QR (Cdqrls); this restatement solves the same normal equations by a
- * long-double Cholesky, which agrees to rounding on the well-conditioned designs used here.
+ * Each step is solved as R does (Cdqrls: rows scaled by sqrt(w), Householder QR, qr_ls above).
  * x: n*p col-major WITHOUT intercept; coef[p+1]: (Intercept) first, then the columns of x.
  * Returns 0 if converged, 1 otherwise.
  */
@@ -1243,8 +1406,7 @@ ORC_API int orc_glm_binomial(long n, int p, const double *x, const double *y, in
                              double epsilon, double *coef, double *deviance, int *iters) {
     const int q = p + 1;
     double *eta = (double *)malloc(sizeof(double) * n), *mu = (double *)malloc(sizeof(double) * n);
-    long double *A = (long double *)malloc(sizeof(long double) * q * q);
-    long double *b = (long double *)malloc(sizeof(long double) * q);
+    double *Xw = (double *)malloc(sizeof(double) * (size_t)n * q), *zw = (double *)malloc(sizeof(double) * n);
     for (long i = 0; i < n; ++i) {
         mu[i] = (y[i] + 0.5) / 2.0;
         eta[i] = log(mu[i] / (1.0 - mu[i]));
@@ -1252,40 +1414,19 @@ ORC_API int orc_glm_binomial(long n, int p, const double *x, const double *y, in
     double devold = binom_dev(n, y, mu), dev = devold;
     int conv = 0, it = 0;
     for (it = 1; it <= maxit; ++it) {
-        for (int a = 0; a < q * q; ++a) A[a] = 0.0L;
-        for (int a = 0; a < q; ++a) b[a] = 0.0L;
         for (long i = 0; i < n; ++i) {
             const double w = mu[i] * (1.0 - mu[i]);
             const double z = eta[i] + (y[i] - mu[i]) / w;
-            /* row (1, x_i) */
-            for (int a = 0; a < q; ++a) {
-                const double xa = a == 0 ? 1.0 : x[(size_t)(a - 1) * n + i];
-                b[a] += (long double)w * xa * z;
-                for (int c = 0; c <= a; ++c) {
-                    const double xc = c == 0 ? 1.0 : x[(size_t)(c - 1) * n + i];
-                    A[a * q + c] += (long double)w * xa * xc;
-                }
-            }
+            const double sw = sqrt(w);
+            Xw[i] = sw;
+            for (int a = 1; a < q; ++a) Xw[(size_t)a * n + i] = sw * x[(size_t)(a - 1) * n + i];
+            zw[i] = sw * z;
         }
-        /* Cholesky A = L L^T (lower), solve */
-        for (int a = 0; a < q; ++a) {
-            for (int c = 0; c <= a; ++c) {
-                long double s = A[a * q + c];
-                for (int k = 0; k < c; ++k) s -= A[a * q + k] * A[c * q + k];
-                A[a * q + c] = (a == c) ? sqrtl(s) : s / A[c * q + c];
-            }
+        const int rank = qr_ls(n, q, Xw, zw, fmin(1e-7, epsilon / 1000.0) /* glm.fit: min(1e-07, control$epsilon/1000) */, coef, NULL);
+        if (rank < q) { /* glm would carry NA coefficients on; this path treats it as a failure */
+            free(eta); free(mu); free(Xw); free(zw);
+            return 2;
         }
-        for (int a = 0; a < q; ++a) {
-            long double s = b[a];
-            for (int k = 0; k < a; ++k) s -= A[a * q + k] * b[k];
-            b[a] = s / A[a * q + a];
-        }
-        for (int a = q - 1; a >= 0; --a) {
-            long double s = b[a];
-            for (int k = a + 1; k < q; ++k) s -= A[k * q + a] * b[k];
-            b[a] = s / A[a * q + a];
-        }
-        for (int a = 0; a < q; ++a) coef[a] = (double)b[a];
         for (long i = 0; i < n; ++i) {
             double e = coef[0];
             for (int a = 1; a < q; ++a) e += coef[a] * x[(size_t)(a - 1) * n + i];
@@ -1301,6 +1442,6 @@ ORC_API int orc_glm_binomial(long n, int p, const double *x, const double *y, in
     }
     *deviance = dev;
     *iters = it > maxit ? maxit : it;
-    free(eta); free(mu); free(A); free(b);
+    free(eta); free(mu); free(Xw); free(zw);
     return conv ? 0 : 1;
 }

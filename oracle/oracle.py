@@ -268,3 +268,22 @@ def glm_binomial(x, y, maxit=25, epsilon=1e-8):
     rc = lib().orc_glm_binomial(C.c_long(n), C.c_int(p), _d(x), _d(y), C.c_int(maxit), C.c_double(epsilon),
                                 _d(coef), C.byref(dev), C.byref(it))
     return dict(coef=coef, deviance=dev.value, iters=it.value, converged=(rc == 0))
+
+
+def lm(x, y, weights=None, want_resid=False):
+    """stats::lm(y ~ x[, weights]) + summary(): coef/std_err [(Intercept), x...] (NaN = NA), sigma, rss,
+    rank, df_residual, resid."""
+    x = _f(x)
+    y = _v(y)
+    n, p = x.shape
+    w = _v(weights)
+    coef = np.zeros(p + 1)
+    se = np.zeros(p + 1)
+    sigma = C.c_double(0)
+    rss = C.c_double(0)
+    rdf = C.c_long(0)
+    resid = np.empty(n) if want_resid else None
+    rank = lib().orc_lm(C.c_long(n), C.c_int(p), _d(x), _d(y), _d(w), _d(coef), _d(se), C.byref(sigma),
+                        C.byref(rss), C.byref(rdf), _d(resid))
+    return dict(coef=coef, std_err=se, sigma=sigma.value, rss=rss.value, rank=rank, df_residual=rdf.value,
+                resid=resid)

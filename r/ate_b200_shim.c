@@ -150,12 +150,35 @@ SEXP C_ate_crossfit_aipw(SEXP ctx, SEXP x, SEXP w, SEXP y, SEXP K, SEXP B, SEXP 
     return out;
 }
 
+/* lm() + summary(lm)$coefficients  -- ate_functions.R:25-34, 52-56, 72-81, 320-323.
+ * x: model matrix without "(Intercept)"; weights: numeric or NULL.  Returns a (p+1) x 2 matrix
+ * (Estimate, Std. Error; NA for aliased columns) with attributes sigma, rss, rank, df, residuals. */
+SEXP C_ate_lm(SEXP ctx, SEXP x, SEXP y, SEXP weights, SEXP want_resid) {
+    ate_ctx *c = ctx_of(ctx);
+    const int n = Rf_nrows(x), p = Rf_ncols(x), wr = Rf_asLogical(want_resid);
+    SEXP tab = PROTECT(Rf_allocMatrix(REALSXP, p + 1, 2));
+    SEXP res = PROTECT(wr ? Rf_allocVector(REALSXP, n) : R_NilValue);
+    double sigma, rss; int rank; long long df;
+    int rc = ate_lm(c, n, p, REAL(x), REAL(y), Rf_isNull(weights) ? NULL : REAL(weights), REAL(tab),
+                    REAL(tab) + (p + 1), &sigma, &rss, &rank, &df, wr ? REAL(res) : NULL);
+    FAIL_IF(rc, c, "ate_lm");
+    for (int i = 0; i < 2 * (p + 1); ++i) if (ISNAN(REAL(tab)[i])) REAL(tab)[i] = NA_REAL;
+    Rf_setAttrib(tab, Rf_install("sigma"), Rf_ScalarReal(sigma));
+    Rf_setAttrib(tab, Rf_install("rss"), Rf_ScalarReal(rss));
+    Rf_setAttrib(tab, Rf_install("rank"), Rf_ScalarInteger(rank));
+    Rf_setAttrib(tab, Rf_install("df"), Rf_ScalarReal((double)df));
+    if (wr) Rf_setAttrib(tab, Rf_install("residuals"), res);
+    UNPROTECT(2);
+    return tab;
+}
+
 static const R_CallMethodDef call_methods[] = {
     {"C_ate_ctx_create", (DL_FUNC)&C_ate_ctx_create, 1},
     {"C_ate_cv_glmnet", (DL_FUNC)&C_ate_cv_glmnet, 8},
     {"C_ate_predict", (DL_FUNC)&C_ate_predict, 5},
     {"C_ate_aipw_score", (DL_FUNC)&C_ate_aipw_score, 6},
     {"C_ate_glm_binomial", (DL_FUNC)&C_ate_glm_binomial, 3},
+    {"C_ate_lm", (DL_FUNC)&C_ate_lm, 5},
     {"C_ate_bootstrap", (DL_FUNC)&C_ate_bootstrap, 9},
     {"C_ate_tau_hat_dr_est", (DL_FUNC)&C_ate_tau_hat_dr_est, 7},
     {"C_ate_standardize", (DL_FUNC)&C_ate_standardize, 2},

@@ -61,6 +61,65 @@ tau_hat_dr_est <- function(w, y, p, tauhat0x, tauhat1x) {
   data.frame(Method = method, ATE = tau_hat, lower_ci = tau_hat - se_hat * 1.96, upper_ci = tau_hat + se_hat * 1.96)
 }
 
+# coef(glmnet.fit, s = s): linear interpolation in lambda (glmnet's lambda.interp)
+.coef_at <- function(model, s) {
+  lam <- model$lambda; k <- length(lam)
+  if (s >= lam[1]) return(model$beta[, 1]); if (s <= lam[k]) return(model$beta[, k])
+  sfrac <- (lam[1] - s) / (lam[1] - lam[k]); lamf <- (lam[1] - lam) / (lam[1] - lam[k])
+  coord <- approx(lamf, seq(lam), sfrac)$y; left <- floor(coord); right <- ceiling(coord)
+  if (left == right) return(model$beta[, left])
+  f <- (sfrac - lamf[right]) / (lamf[left] - lamf[right])
+  model$beta[, left] * f + model$beta[, right] * (1 - f)
+}
+
+# lm() %>% summary() %>% coef() for the regression estimators: rows named like R names them
+.lm_b200 <- function(x, y, weights = NULL, resid = FALSE) {
+  tab <- .Call("C_ate_lm", ate_ctx(), x, as.double(y), weights, resid)
+  dimnames(tab) <- list(c("(Intercept)", colnames(x)), c("Estimate", "Std. Error"))
+  tab
+}
+.ci_row <- function(method, tau_hat, se_hat)
+  data.frame(Method = method, ATE = tau_hat, lower_ci = tau_hat - se_hat * 1.96, upper_ci = tau_hat + se_hat * 1.96)
+
+# ate_functions.R:24-39
+ate_condmean_ols <- function(dataset, treatment_var, outcome_var, method = "Direct Method") {
+  x <- model.matrix(~ ., dataset[, names(dataset) != outcome_var])[, -1, drop = FALSE]
+  reg_coef <- .lm_b200(x, dataset[, outcome_var])
+  .ci_row(method, reg_coef[treatment_var, "Estimate"], reg_coef[treatment_var, "Std. Error"])
+}
+
+# ate_functions.R:44-64
+prop_score_weight <- function(dataset, p, treatment_var, outcome_var, covariates, method = "Propensity_Weighting") {
+  w <- dataset[, treatment_var]; y <- dataset[, outcome_var]
+  tau_i <- ((w - p) * y) / (p * (1 - p)); ps_er <- w - p
+  d <- as.matrix(dataset[, covariates] * ps_er)
+  rss <- attr(.lm_b200(d, tau_i), "rss")                       # e <- residuals(summary(lm(tau_hat ~ .)))
+  .ci_row(method, mean(tau_i), sqrt(rss / NROW(dataset)) / sqrt(NROW(dataset)))
+}
+
+# ate_functions.R:67-86
+prop_score_ols <- function(dataset, p, treatment_var, outcome_var, method = "Propensity_Regression") {
+  w <- dataset[, treatment_var]
+  weights <- (w / p) + ((1 - w) / (1 - p))
+  x <- matrix(w, ncol = 1, dimnames = list(NULL, treatment_var))
+  reg_coef <- .lm_b200(x, dataset[, outcome_var], as.double(weights))
+  .ci_row(method, reg_coef[treatment_var, "Estimate"], reg_coef[treatment_var, "Std. Error"])
+}
+
+# ate_functions.R:286-328 -- expansion, both cv.glmnet fits and the post-lasso OLS on the library
+belloni <- function(dataset, treatment_var, outcome_var, method = "Belloni et.al") {
+  x <- .Call("C_ate_expand_deg2", ate_ctx(), as.matrix(dataset[, covariates]), TRUE)      # :288-296 (+ mains)
+  w <- as.matrix(dataset[treatment_var]); y <- as.matrix(dataset[outcome_var])
+  model_xw <- .cv_glmnet_b200(x, w, 0L); model_xy <- .cv_glmnet_b200(x, y, 0L)            # :304-305
+  s <- model_xw$lambda[model_xw$idx.min]
+  c_xw <- model_xw$beta[, model_xw$idx.min]; c_xy <- .coef_at(model_xy, s)                # :308-309
+  c_union <- unique(c(which(c_xw > 0), which(c_xy > 0))) - 1                              # :312-314
+  x_restricted <- cbind(x[, c_union], w); colnames(x_restricted) <- NULL                 # :317
+  reg_coef <- .lm_b200(x_restricted, y)                                                   # :320
+  k <- nrow(reg_coef)                                                                     # the "x_restrictedW" row
+  .ci_row(method, reg_coef[k, "Estimate"], reg_coef[k, "Std. Error"])
+}
+
 # ate_functions.R:211-264 -- same formals; only the two glm() calls and the tail change
 doubly_robust_glm <- function(dataset, treatment_var, outcome_var, bootstrap_se = F) {
   mm <- function(d) model.matrix(~ ., d)[, -1, drop = FALSE]          # what glm builds for `~ .`

@@ -192,3 +192,28 @@ def test_glm_binomial_is_the_mle_and_matches_glm_fit_conventions(oracle):
     assert np.abs(path["beta"][:, -1] - g["coef"][1:]).max() < 1e-4
     # maxit = 1 reports non-convergence, like R's warning
     assert not oracle.glm_binomial(x, y, maxit=1)["converged"]
+
+
+def test_lm_qr_matches_normal_equations_and_summary_formulas(oracle):
+    """stats::lm + summary.lm as the regression estimators use them (ate_functions.R:28, 53, 74, 320):
+    Estimate, Std. Error = sqrt(rss/rdf * diag((X'WX)^-1)), zero weights leave the df, aliased columns
+    come back NA in dqrdc2's order (later duplicates are the ones dropped)."""
+    rng = np.random.default_rng(0)
+    n, p = 500, 6
+    x = rng.standard_normal((n, p))
+    y = x @ rng.standard_normal(p) + 0.5 + rng.standard_normal(n)
+    w = rng.uniform(0.5, 2, n); w[:7] = 0
+    for ww in (None, w):
+        r = oracle.lm(x, y, ww, want_resid=True)
+        xa = np.column_stack([np.ones(n), x]); W = np.ones(n) if ww is None else ww
+        xtx = xa.T @ (W[:, None] * xa)
+        b = np.linalg.solve(xtx, xa.T @ (W * y))
+        e = y - xa @ b
+        rss, df = (W * e * e).sum(), int((W != 0).sum()) - p - 1
+        assert np.abs(r["coef"] - b).max() < 1e-12 and r["df_residual"] == df and r["rank"] == p + 1
+        assert np.abs(r["std_err"] - np.sqrt(rss / df * np.diag(np.linalg.inv(xtx)))).max() < 1e-12
+        assert np.abs(r["resid"] - e).max() < 1e-11
+    x2 = np.column_stack([x[:, :3], x[:, 0], x[:, 3:], np.zeros(n)])
+    r2, r0 = oracle.lm(x2, y), oracle.lm(x, y)
+    assert np.isnan(r2["coef"][[4, 8]]).all() and r2["rank"] == p + 1
+    assert np.abs(r2["coef"][[0, 1, 2, 3, 5, 6, 7]] - r0["coef"]).max() < 1e-12
