@@ -21,11 +21,20 @@
 //              memory (second mbarrier) for the MMA and helper warps.
 //   helpers  : (lead CTA of a row chunk) accumulate X^T r, X^T v on the FP64 FMA pipe from the
 //              same staged rows -- off the eval warps' critical path and off the tensor pipe.
-//   MMA      : as gram.cu -- one 32x32 block of the lower triangle per warp, operands gathered from
-//              the staged rows through the column list.
+//   MMA      : the lower triangle of H in 8x8 tiles.  A warp owns up to four tile ROWS of one
+//              32-column segment (<= 16 tiles, 64 accumulator registers); a host-built plan deals
+//              the tile rows of every list width over the warps so that the busiest warp carries
+//              as few tiles as possible -- one warp issues a DMMA.8x8x4 only every ~33 cycles, so a
+//              64-column list as three 32x32 blocks (64 DMMA per slot on one warp) was issue-bound
+//              at 0.65 of HBM speed; dealt by tile rows it needs 20.  Operands are gathered from the
+//              staged rows through the column list.
 // Row chunks are folded in fixed order afterwards: bit-reproducible.
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
+
+#include <vector>
 
 #include "irls_step.cuh"
 #include "path.cuh"
@@ -60,9 +69,80 @@ struct StepArgs {
     const double *coef;
     double w;
     const int *colidx;
+    const uint2 *plan;  // this launch's tile-row plan: one descriptor per MMA warp of the grid row
     int nblk, stages;
     double *gram_partials, *eval_partials, *v_out;
+    int trace;                // -DATE_STEP_TRACE builds: stamp this launch (value = list width)
+    unsigned long long *dbg;  // ATE_STEP_WATCHDOG=1: host-mapped log of barrier waits that never end
 };
+
+// mbar_wait with a deadlock detector: when a log buffer is given, a wait that lasts longer than two
+// seconds (a launch takes under a millisecond) writes who waits on what, and one second later traps.
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __noinline__ void wait_report(unsigned long long *dbg, int tag, int it, int s, uint32_t parity,
+                                        unsigned long long info) {
+    if ((threadIdx.x & 31) == 0) {
+        const unsigned long long k = atomicAdd(dbg, 1ull);
+        if (k < 120) {
+            dbg[4 + 4 * k] = (unsigned long long)tag | ((unsigned long long)(threadIdx.x >> 5) << 8) |
+                             ((unsigned long long)blockIdx.x << 16) | ((unsigned long long)blockIdx.y << 32);
+            dbg[5 + 4 * k] = (unsigned long long)(unsigned)it;
+            dbg[6 + 4 * k] = (unsigned long long)(unsigned)s | ((unsigned long long)parity << 32);
+            dbg[7 + 4 * k] = info;
+        }
+        __threadfence_system();
+    }
+}
+__device__ __forceinline__ void wait_w(uint64_t *bar, uint32_t parity, const StepArgs &a, int tag, int it, int s) {
+    unsigned long long *dbg = a.dbg;
+    if (dbg == nullptr) {
+        mbar_wait(bar, parity);
+        return;
+    }
+    unsigned long long t0 = 0;
+    bool reported = false;
+    for (unsigned spins = 0;; ++spins) {
+        uint32_t done;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (done) return;
+        if ((spins & 255u) == 255u) {
+            const unsigned long long t = gtimer_ns();
+            if (t0 == 0) t0 = t;
+            if (!reported && t - t0 > 2000000000ull) {
+                wait_report(dbg, tag, it, s, parity,
+                            (unsigned long long)(unsigned)a.ncols | ((unsigned long long)(unsigned)a.stages << 16) |
+                                ((unsigned long long)(unsigned)a.nblk << 24) |
+                                ((unsigned long long)(a.rows == nullptr && a.ld == (long long)(a.ncols + F_PAD)) << 40) |
+                                ((unsigned long long)(a.rows_per_chunk / F_ROWS) << 41));
+                reported = true;
+            }
+            if (t - t0 > 3000000000ull) __trap();
+        }
+    }
+}
+
+// -DATE_STEP_TRACE: CTA (0,0) of launches with a narrow list stamps clock64() per slot and role into
+// a device buffer (tools/step_trace.py prints the timeline).  Compiled out otherwise.
+#ifdef ATE_STEP_TRACE
+constexpr int TR_SLOTS = 96, TR_EVENTS = 12;
+__device__ long long g_trace[TR_SLOTS * TR_EVENTS + 8];
+#define TRACE(ev, it)                                                                         \
+    do {                                                                                      \
+        if (trace_on && (it) < TR_SLOTS && (threadIdx.x & 31) == 0) g_trace[8 + (it) * TR_EVENTS + (ev)] = clock64(); \
+    } while (0)
+#else
+#define TRACE(ev, it) do { } while (0)
+#endif
 
 template <int ITER, bool INIT>
 __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs a) {
@@ -76,6 +156,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
     uint64_t *vfull = full + stages, *empty = vfull + stages;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef ATE_STEP_TRACE
+    const bool trace_on = blockIdx.x == 0 && blockIdx.y == 0 && a.trace != 0;
+    if (trace_on && threadIdx.x == 0) {
+        g_trace[0] = clock64(); g_trace[1] = a.ncols; g_trace[2] = a.stages; g_trace[3] = a.nblk;
+        g_trace[4] = a.rows_per_chunk / F_ROWS; g_trace[5] = a.trace;
+    }
+#endif
     const long long c_begin = (long long)blockIdx.y * a.rows_per_chunk;
     long long c_rows = a.nrows - c_begin;
     if (c_rows > a.rows_per_chunk) c_rows = a.rows_per_chunk;
@@ -111,7 +198,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 const uint32_t ph = (uint32_t)(it / stages) & 1u;
                 const long long t0 = c_begin + (long long)it * F_ROWS;
                 const int cnt = (int)((c_end - t0) < F_ROWS ? (c_end - t0) : F_ROWS);
-                mbar_wait(empty + s, ph ^ 1u);
+                wait_w(empty + s, ph ^ 1u, a, 1, it, s);
+                TRACE(0, it);  // producer: slot free
                 double *dst0 = sx + stage_doubles * s;
                 if (lane < F_ROWS) {
                     sv[s * F_ROWS + lane] = lane < cnt ? 1.0 : 0.0;
@@ -160,7 +248,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 ring_ok[d] = fetch(it + F_PF * F_PWARPS, ring_r[d]);
                 const int s = it % stages;
                 const uint32_t ph = (uint32_t)(it / stages) & 1u;
-                mbar_wait(empty + s, ph ^ 1u);
+                wait_w(empty + s, ph ^ 1u, a, 2, it, s);
                 double *dst = sx + stage_doubles * s + (size_t)lane * pitch;
                 if (lane < F_ROWS) {
                     sv[s * F_ROWS + lane] = cur_ok ? 1.0 : 0.0;
@@ -194,7 +282,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
         for (int it = e; it < nit; it += F_EWARPS) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
-            mbar_wait(full + s, ph);
+            wait_w(full + s, ph, a, 3, it, s);
+            TRACE(1, it);  // eval: rows landed
             const double *base = sx + stage_doubles * s;
             double part[F_ROWS];
 #pragma unroll
@@ -238,6 +327,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 sy[s * F_ROWS + rr] = ri;
             }
             __syncwarp();
+            TRACE(2, it);  // eval: v, r ready
             if (lane == 0) {
                 mbar_arrive(vfull + s);  // MMA and helper warps may start on this slot
                 mbar_arrive(empty + s);  // ... and this warp is done with its staged rows
@@ -281,9 +371,10 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
         for (int it = h; it < nit; it += F_HWARPS) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
-            mbar_wait(full + s, ph);
+            wait_w(full + s, ph, a, 4, it, s);
             if (lead) {
-                mbar_wait(vfull + s, ph);
+                wait_w(vfull + s, ph, a, 5, it, s);
+                TRACE(3, it);  // helper: start
                 const double *base = sx + stage_doubles * s;
 #pragma unroll 4
                 for (int q2 = 0; q2 < F_ROWS; ++q2) {
@@ -308,6 +399,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 }
             }
             __syncwarp();
+            TRACE(4, it);  // helper: done
             if (lane == 0) mbar_arrive(empty + s);
         }
         if (lead) {
@@ -327,30 +419,31 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
         }
     } else {
         // ------------------------------ MMA ------------------------------
-        const int q = blockIdx.x * F_CWARPS + warp;
-        const bool active = q < a.nblk;
-        int bi = 0, bj = 0;
-        if (active) tri_block(q, bi, bj);
-        const bool diag = (bi == bj);
+        // descriptor: x = segment | count << 8, y = four tile-row numbers (bytes)
+        const uint2 d = __ldg(a.plan + blockIdx.x * F_CWARPS + warp);
+        const int seg = (int)(d.x & 0xffu), cnt = (int)((d.x >> 8) & 0xffu);
+        const int g = lane >> 2, k4 = lane & 3;
+        int tr[4], nt[4], offA[4], offB[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            tr[u] = (int)((d.y >> (8 * u)) & 0xffu);
+            const int lim = tr[u] - 4 * seg + 1;  // tiles left of (and on) the diagonal in this segment
+            nt[u] = u < cnt ? (lim < 4 ? lim : 4) : 0;
+            offA[u] = nt[u] > 0 ? __ldg(a.colidx + tr[u] * 8 + g) : 0;
+            offB[u] = cnt > 0 ? __ldg(a.colidx + (4 * seg + u) * 8 + g) : 0;
+        }
         double acc[4][4][2];
 #pragma unroll
-        for (int m = 0; m < 4; ++m)
+        for (int u = 0; u < 4; ++u)
 #pragma unroll
-            for (int n = 0; n < 4; ++n) acc[m][n][0] = acc[m][n][1] = 0.0;
-        const int g = lane >> 2, k4 = lane & 3;
-        int offA[4], offB[4];
-#pragma unroll
-        for (int m = 0; m < 4; ++m) {
-            const int ia = bi * 32 + m * 8 + g, ib = bj * 32 + m * 8 + g;
-            offA[m] = active ? __ldg(a.colidx + ia) : 0;
-            offB[m] = active ? __ldg(a.colidx + ib) : 0;
-        }
+            for (int n = 0; n < 4; ++n) acc[u][n][0] = acc[u][n][1] = 0.0;
         for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
-            mbar_wait(full + s, ph);
-            mbar_wait(vfull + s, ph);
-            if (active) {
+            wait_w(full + s, ph, a, 6, it, s);
+            wait_w(vfull + s, ph, a, 7, it, s);
+            if (warp < 3) TRACE(5 + 2 * warp, it);  // MMA warp 0..2: start
+            if (cnt > 0) {
                 const double *base = sx + stage_doubles * s;
                 const double *vs = sv + s * F_ROWS;
 #pragma unroll
@@ -360,29 +453,33 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                     const double vv = vs[r];
                     double fa[4], fb[4];
 #pragma unroll
-                    for (int m = 0; m < 4; ++m) fa[m] = rowp[offA[m]];
+                    for (int u = 0; u < 4; ++u) fa[u] = nt[u] > 0 ? rowp[offA[u]] : 0.0;
 #pragma unroll
-                    for (int m = 0; m < 4; ++m) fb[m] = rowp[offB[m]] * vv;
+                    for (int n = 0; n < 4; ++n) fb[n] = rowp[offB[n]] * vv;
 #pragma unroll
-                    for (int m = 0; m < 4; ++m)
+                    for (int u = 0; u < 4; ++u)
 #pragma unroll
                         for (int n = 0; n < 4; ++n)
-                            if (!diag || n <= m)  // a diagonal block only needs its lower 8x8 tiles
-                                dmma884(acc[m][n][0], acc[m][n][1], fa[m], fb[n]);
+                            if (n < nt[u]) dmma884(acc[u][n][0], acc[u][n][1], fa[u], fb[n]);
                 }
             }
             __syncwarp();
+            if (warp < 3) TRACE(6 + 2 * warp, it);  // MMA warp 0..2: done
             if (lane == 0) mbar_arrive(empty + s);
         }
-        if (active) {
-            double *out = a.gram_partials + ((size_t)blockIdx.y * a.nblk + q) * 1024;
+        // tile (tr[u], 4 seg + n) sits in 32x32 block (tr[u] / 4, seg) of the fold kernel's layout
 #pragma unroll
-            for (int m = 0; m < 4; ++m)
+        for (int u = 0; u < 4; ++u) {
+            if (nt[u] > 0) {
+                const int bi = tr[u] >> 2, m = tr[u] & 3;
+                double *out = a.gram_partials + ((size_t)blockIdx.y * a.nblk + (bi * (bi + 1) / 2 + seg)) * 1024;
 #pragma unroll
-                for (int n = 0; n < 4; ++n) {
-                    const int r = m * 8 + g, c = n * 8 + 2 * k4;
-                    *reinterpret_cast<double2 *>(out + r * 32 + c) = make_double2(acc[m][n][0], acc[m][n][1]);
-                }
+                for (int n = 0; n < 4; ++n)
+                    if (n < nt[u]) {
+                        const int r = m * 8 + g, c = n * 8 + 2 * k4;
+                        *reinterpret_cast<double2 *>(out + r * 32 + c) = make_double2(acc[u][n][0], acc[u][n][1]);
+                    }
+            }
         }
     }
 }
@@ -413,6 +510,120 @@ int launch_step(ate_ctx *ctx, const StepArgs &a, dim3 grid, size_t smem, bool in
     return 0;
 }
 
+// ---- tile-row plan -------------------------------------------------------------------------
+// For a list of ntr = ceil(nG / 8) tile rows: segment s (columns 32 s .. 32 s + 31 of the list) holds
+// tile rows r >= 4 s with min(4, r - 4 s + 1) tiles each.  A warp takes <= 4 tile rows of ONE segment
+// (they share the four B operands).  Rows are packed first-fit-decreasing under a load bound T; the
+// smallest feasible T over the 8 * ngroups warps wins, and ngroups grows only when 16 tiles per warp
+// are not enough.  Built once per process, copied once per ctx.
+constexpr int F_MAX_NTR = 52;   // 416 list columns, the widest row the staging ring holds
+constexpr int F_PLAN_W = 128;   // descriptor slots per width
+
+struct StepPlan {
+    int ngroups[F_MAX_NTR + 1];
+    int max_tiles[F_MAX_NTR + 1];
+    std::vector<uint2> tab;
+    int min_tiles = 16;  // measured on B200: spreading a narrow list over more MMA warps is slower (the warps
+                         // contend for shared-memory reads), so rows are packed block-like; ATE_PLAN_MINT overrides
+    StepPlan() : tab((size_t)(F_MAX_NTR + 1) * F_PLAN_W, make_uint2(0u, 0u)) {
+        if (const char *e = getenv("ATE_PLAN_MINT")) min_tiles = atoi(e);
+        ngroups[0] = 1;
+        max_tiles[0] = 0;
+        for (int ntr = 1; ntr <= F_MAX_NTR; ++ntr) build(ntr);
+    }
+    static int pack(int ntr, int T, std::vector<uint2> *out) {
+        int bins = 0;
+        const int nseg = (ntr + 3) / 4;
+        for (int sgm = 0; sgm < nseg; ++sgm) {
+            struct Bin { int load, cnt, rows[4]; };
+            std::vector<Bin> b;
+            // tile rows of this segment by decreasing cost: the full ones (4 tiles), then 4 s + 3 .. 4 s
+            std::vector<int> order;
+            for (int r = 4 * sgm + 3; r < ntr; ++r) order.push_back(r);
+            for (int r = (4 * sgm + 2 < ntr - 1 ? 4 * sgm + 2 : ntr - 1); r >= 4 * sgm; --r) order.push_back(r);
+            for (int r : order) {
+                const int c = r - 4 * sgm + 1 < 4 ? r - 4 * sgm + 1 : 4;
+                size_t k = 0;
+                for (; k < b.size(); ++k)
+                    if (b[k].cnt < 4 && b[k].load + c <= T) break;
+                if (k == b.size()) b.push_back(Bin{0, 0, {0, 0, 0, 0}});
+                b[k].rows[b[k].cnt++] = r;
+                b[k].load += c;
+            }
+            for (const Bin &x : b) {
+                if (out)
+                    out->push_back(make_uint2((unsigned)sgm | ((unsigned)x.cnt << 8),
+                                              (unsigned)x.rows[0] | ((unsigned)x.rows[1] << 8) |
+                                                  ((unsigned)x.rows[2] << 16) | ((unsigned)x.rows[3] << 24)));
+                ++bins;
+            }
+        }
+        return bins;
+    }
+    void build(int ntr) {
+        const int total = ntr * (ntr + 1) / 2;
+        for (int g = 1; 8 * g <= F_PLAN_W; ++g) {
+            const int W = 8 * g;
+            int T0 = (total + W - 1) / W;
+            if (T0 < min_tiles) T0 = min_tiles;
+            for (int T = T0; T <= 16; ++T) {
+                if (T < 4 && ntr >= 4) continue;  // a full tile row is 4 tiles
+                if (pack(ntr, T, nullptr) <= W) {
+                    std::vector<uint2> d;
+                    pack(ntr, T, &d);
+                    for (size_t k = 0; k < d.size(); ++k) tab[(size_t)ntr * F_PLAN_W + k] = d[k];
+                    ngroups[ntr] = g;
+                    max_tiles[ntr] = T;
+                    return;
+                }
+            }
+        }
+        ngroups[ntr] = -1;
+        max_tiles[ntr] = -1;
+    }
+};
+
+// ATE_STEP_WATCHDOG=1: a host-mapped log the kernel's barrier waits report into (see wait_w); printed
+// at process exit when anything was reported.  Off by default: the kernel then uses the plain wait.
+unsigned long long *g_wd_host = nullptr, *g_wd_dev = nullptr;
+void wd_print() {
+    if (!g_wd_host || g_wd_host[0] == 0) return;
+    static const char *names[] = {"?", "producer(slot copy)/empty", "producer(row copies)/empty", "eval/full", "helper/full",
+                                  "helper/vfull", "mma/full", "mma/vfull"};
+    fprintf(stderr, "[ate] irls_step_kernel: %llu barrier waits never completed:\n", g_wd_host[0]);
+    const unsigned long long n = g_wd_host[0] < 120 ? g_wd_host[0] : 120;
+    for (unsigned long long k = 0; k < n; ++k) {
+        const unsigned long long w = g_wd_host[4 + 4 * k], it = g_wd_host[5 + 4 * k], sp = g_wd_host[6 + 4 * k];
+        const unsigned long long in = g_wd_host[7 + 4 * k];
+        fprintf(stderr, "  cta(%llu,%llu) warp %2llu %-28s slot %llu stage %llu parity %llu | ncols %llu stages %llu nblk %llu "
+                        "contiguous %llu slots/chunk %llu\n",
+                (w >> 16) & 0xffff, w >> 32, (w >> 8) & 0xff, names[w & 0xff], it, sp & 0xffffffffu, sp >> 32, in & 0xffff,
+                (in >> 16) & 0xff, (in >> 24) & 0xffff, (in >> 40) & 1, in >> 41);
+    }
+}
+unsigned long long *watchdog_buffer() {
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        const char *e = getenv("ATE_STEP_WATCHDOG");
+        if (e && atoi(e) != 0) {
+            void *h = nullptr, *d = nullptr;
+            if (cudaHostAlloc(&h, 4096, cudaHostAllocMapped) == cudaSuccess && cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) {
+                memset(h, 0, 4096);
+                g_wd_host = (unsigned long long *)h;
+                g_wd_dev = (unsigned long long *)d;
+                atexit(wd_print);
+            }
+        }
+    }
+    return g_wd_dev;
+}
+
+const StepPlan &step_plan() {
+    static const StepPlan plan;
+    return plan;
+}
+
 }  // namespace
 
 int ate_i_irls_step(ate_ctx *ctx, const IrlsStep &in) {
@@ -428,7 +639,17 @@ int ate_i_irls_step(ate_ctx *ctx, const IrlsStep &in) {
     if (stages > F_MAX_STAGES) stages = F_MAX_STAGES;
     if (stages < 2) return ate_fail(ctx, -1, "irls_step: %d staged columns do not fit the full-row kernel", ncols);
     const size_t smem = stages * stage_bytes + 3 * stages * sizeof(uint64_t);
-    const int ngroups = nblk > 0 ? (nblk + F_CWARPS - 1) / F_CWARPS : 1;
+    const int ntr = (nG + 7) / 8;
+    if (ntr > F_MAX_NTR) return ate_fail(ctx, -1, "irls_step: a %d-column list exceeds the tile plan", nG);
+    const StepPlan &plan = step_plan();
+    const int ngroups = plan.ngroups[ntr];
+    if (ngroups < 1) return ate_fail(ctx, -1, "irls_step: no tile plan for %d list columns", nG);
+    const bool plan_fresh = ctx->cache.find("irls.plan") == ctx->cache.end();
+    void *dplan = nullptr;
+    ATE_TRY(ate_cached(ctx, "irls.plan", sizeof(uint2) * plan.tab.size(), &dplan));
+    if (plan_fresh)
+        ATE_CUDA(ctx, cudaMemcpyAsync(dplan, plan.tab.data(), sizeof(uint2) * plan.tab.size(), cudaMemcpyHostToDevice,
+                                      ctx->stream));
     int nchunks = ctx->num_sms / ngroups;
     if (nchunks < 1) nchunks = 1;
     long long max_chunks = (in.nrows + 4 * F_ROWS - 1) / (4 * F_ROWS);
@@ -450,9 +671,39 @@ int ate_i_irls_step(ate_ctx *ctx, const IrlsStep &in) {
     a.rows_per_chunk = rpc;
     a.ni = in.ni; a.iy = in.iy; a.coef = in.coef; a.w = in.w;
     a.colidx = in.colidx; a.nblk = nblk; a.stages = stages;
+    a.plan = (const uint2 *)dplan + (size_t)ntr * F_PLAN_W;
     a.gram_partials = (double *)scr;
     a.eval_partials = (double *)scr + gram_doubles;
     a.v_out = in.v_out;
+    a.dbg = watchdog_buffer();
+    a.trace = 0;
+#ifdef ATE_STEP_TRACE
+    {
+        static const char *want = getenv("ATE_STEP_TRACE_NG");  // "lo:hi": stamp launches with lo <= nG <= hi
+        int lo = 33, hi = 64;
+        if (want) sscanf(want, "%d:%d", &lo, &hi);
+        if (nG >= lo && nG <= hi && in.nrows > 500000 && ngroups == 1) a.trace = nG;
+        static bool reg = false;
+        if (!reg) {
+            reg = true;
+            atexit([] {
+                static long long h[TR_SLOTS * TR_EVENTS + 8];
+                if (cudaMemcpyFromSymbol(h, g_trace, sizeof(h)) != cudaSuccess) return;
+                const char *path = getenv("ATE_STEP_TRACE_OUT");
+                FILE *f = fopen(path ? path : "step_trace.csv", "w");
+                if (!f) return;
+                fprintf(f, "# ncols %lld stages %lld nblk %lld slots %lld nG %lld\n", h[1], h[2], h[3], h[4], h[5]);
+                fprintf(f, "slot,prod_free,eval_start,eval_done,help_start,help_done,m0_start,m0_done,m1_start,m1_done,m2_start,m2_done\n");
+                for (int it = 0; it < TR_SLOTS; ++it) {
+                    fprintf(f, "%d", it);
+                    for (int e = 0; e < 11; ++e) fprintf(f, ",%lld", h[8 + it * TR_EVENTS + e] ? h[8 + it * TR_EVENTS + e] - h[0] : -1);
+                    fprintf(f, "\n");
+                }
+                fclose(f);
+            });
+        }
+    }
+#endif
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->profile) {
         ATE_CUDA(ctx, cudaEventCreate(&e0));
