@@ -8,26 +8,28 @@
 // HBM-bound kernel (algorithmic bytes: nrows * (ncols + 1) * 8) and the coordinate descent runs
 // on the p x p result (path_binom.cu).
 //
-// CTA = 8 MMA warps + 2 helper warps + 2 producer warps + 4 evaluation warps, one CTA per SM.
-// The working-response refresh is a long dependent chain (dot -> shuffle reduce -> exp -> divide
-// -> log), so it is latency-bound per warp; slots are therefore small (16 rows, up to 6 in flight)
-// and handed to the evaluation warps round-robin: each warp works on every 4th slot and has four
-// slot periods to finish it.
-//   producer : stages 16 rows per slot with 16 one-dimensional TMA bulk copies (one per lane)
-//              into an mbarrier ring, plus y and a validity flag per row.
-//   eval     : lanes hold a column slice of beta; the 16 partial dot products of a slot are
-//              reduce-scattered across the warp (5 exchange steps), so lane l ends up with row
-//              l/2 and the exp/log work of 16 rows runs in parallel lanes.  v and r go to shared
-//              memory (second mbarrier) for the MMA and helper warps.
+// CTA = 8 MMA warps + 2 helper warps + 2 producer warps + 4 evaluation warps, one CTA per SM, around
+// a ring of 32-row slots in shared memory (three at the C1 width of 264 staged columns).  Measured
+// with the per-slot trace (-DATE_STEP_TRACE): every role pays ~1-2 thousand cycles per slot that do
+// not depend on the slot's size (barrier round trips, operand-load latency at the head of the MMA
+// chain), so 16-row slots ran at 2600 cycles per slot whichever way the work was dealt; 32-row
+// slots halve that overhead per row.
+//   producers: producer pw stages rows [16 pw, 16 pw + 16) of every slot with one-dimensional TMA
+//              bulk copies (one per lane; ONE copy for the whole slot when the rows are contiguous
+//              at the slot's pitch) into an mbarrier ring, plus a validity flag per row.
+//   eval     : the working-response refresh is a long dependent chain (dot -> shuffle reduce -> exp
+//              -> divide -> log), latency-bound per warp, so a slot is refreshed by two warps (16
+//              rows each) and consecutive slots by different pairs.  Lanes hold a column slice of
+//              beta; the 16 partial dots are reduce-scattered across the warp (5 exchange steps),
+//              so lane l ends up with row l/2 and the exp/log work of 16 rows runs in parallel
+//              lanes.  v and r go to shared memory (second mbarrier) for the MMA and helper warps.
 //   helpers  : (lead CTA of a row chunk) accumulate X^T r, X^T v on the FP64 FMA pipe from the
-//              same staged rows -- off the eval warps' critical path and off the tensor pipe.
+//              same staged rows, 16 rows of every slot each -- off the eval warps' critical path and
+//              off the tensor pipe.
 //   MMA      : the lower triangle of H in 8x8 tiles.  A warp owns up to four tile ROWS of one
-//              32-column segment (<= 16 tiles, 64 accumulator registers); a host-built plan deals
-//              the tile rows of every list width over the warps so that the busiest warp carries
-//              as few tiles as possible -- one warp issues a DMMA.8x8x4 only every ~33 cycles, so a
-//              64-column list as three 32x32 blocks (64 DMMA per slot on one warp) was issue-bound
-//              at 0.65 of HBM speed; dealt by tile rows it needs 20.  Operands are gathered from the
-//              staged rows through the column list.
+//              32-column segment (<= 16 tiles, 64 accumulator registers), dealt by a host-built plan
+//              for every list width.  Operands are gathered from the staged rows through the
+//              column list.
 // Row chunks are folded in fixed order afterwards: bit-reproducible.
 #include <math.h>
 #include <stdio.h>
@@ -44,20 +46,35 @@ namespace {
 
 using namespace atk;
 
-constexpr int F_ROWS = 16;    // rows per slot: small slots, many of them in flight
+#ifndef ATE_STEP_ROWS
+#define ATE_STEP_ROWS 32
+#endif
+constexpr int F_ROWS = ATE_STEP_ROWS;  // rows per slot (16 or 32)
+constexpr int F_HALF = 16;             // an eval warp refreshes 16 rows at a time (its reduce-scatter is 16 wide)
+constexpr int F_HALVES = F_ROWS / F_HALF;
 constexpr int F_CWARPS = 8;   // MMA warps;  8 + 2 + 2 + 4 = 16 warps: 128 registers per thread
-constexpr int F_HWARPS = 2;   // helper warps (X^T r, X^T v); slot `it` belongs to helper it % 2
-constexpr int F_EWARPS = 4;   // evaluation warps; slot `it` belongs to eval warp it % 4
-constexpr int F_PWARPS = 2;   // producer warps; slot `it` belongs to producer it % 2.  One warp issues a
+constexpr int F_HWARPS = 2;   // helper warps (X^T r, X^T v); each owns an equal share of the rows of every slot
+constexpr int F_EWARPS = 4;   // evaluation warps, taking turns on the slots (see F_TURNS)
+constexpr int F_PWARPS = 2;   // producer warps; each stages an equal share of the rows of every slot.  One warp issues a
                               // 2 KB bulk copy every ~140 cycles (the copies of a warp's lanes are
                               // serialised on the uniform datapath): 4.1 TB/s chip-wide, measured --
                               // two warps lift the issue rate above what HBM delivers
 constexpr int F_THREADS = (F_CWARPS + F_HWARPS + F_PWARPS + F_EWARPS) * 32;
-constexpr int F_PRODUCER = F_CWARPS + F_HWARPS;  // warp index of the first producer
+// Warp w runs on SM sub-partition w % 4.  MMA warps 0-7 (the plan fills 0-3 first), producers 8-9
+// (sub-partitions 0-1, next to the two busiest MMA warps: they hardly compute), helpers 10-11
+// (sub-partitions 2-3), eval warps 12-15 (one per sub-partition).
+constexpr int F_PRODUCER = F_CWARPS;            // warp index of the first producer
+constexpr int F_HELPER = F_CWARPS + F_PWARPS;   // ... of the first helper
+constexpr int F_EVAL = F_HELPER + F_HWARPS;     // ... of the first eval warp
 constexpr int F_PAD = 4;
 constexpr int F_MAX_STAGES = 8;
 constexpr size_t F_SMEM_LIMIT = 227 * 1024;
-static_assert(F_ROWS == 16 && F_HWARPS <= F_EWARPS, "the eval reduce-scatter is written for 16-row slots");
+constexpr int F_PSHARE = F_ROWS / F_PWARPS;  // rows of every slot staged by one producer (one per lane)
+constexpr int F_HSHARE = F_ROWS / F_HWARPS;  // rows of every slot accumulated by one helper
+constexpr int F_TURNS = F_EWARPS / F_HALVES; // eval warp e refreshes half e % F_HALVES of the slots with it % F_TURNS == e / F_HALVES
+static_assert(F_HALF == 16 && (F_ROWS == 16 || F_ROWS == 32) && F_EWARPS % F_HALVES == 0 && F_ROWS % F_PWARPS == 0 &&
+                  F_ROWS % F_HWARPS == 0,
+              "slot geometry");
 
 struct StepArgs {
     const double *X;
@@ -150,8 +167,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
     const int ncols = a.ncols, pitch = ncols + F_PAD, stages = a.stages;
     const size_t stage_doubles = (size_t)F_ROWS * pitch;
     double *sx = reinterpret_cast<double *>(smem_raw);
-    double *sv = sx + stage_doubles * stages;  // [stages][32]: validity from the producer, then v
-    double *sy = sv + (size_t)stages * F_ROWS;  // [stages][F_ROWS]: r from the eval warp
+    double *sv = sx + stage_doubles * stages;   // [stages][F_ROWS]: validity from the producers, then v
+    double *sy = sv + (size_t)stages * F_ROWS;  // [stages][F_ROWS]: r from the eval warps
     uint64_t *full = reinterpret_cast<uint64_t *>(sy + (size_t)stages * F_ROWS);
     uint64_t *vfull = full + stages, *empty = vfull + stages;
 
@@ -175,97 +192,111 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
         sx[(size_t)(e / F_PAD) * pitch + ncols + (e % F_PAD)] = 0.0;  // the list's "zero column"
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
-            mbar_init(full + s, 1);
-            mbar_init(vfull + s, 1);
-            mbar_init(empty + s, F_CWARPS + 2);  // MMA warps + the slot's eval warp + its helper warp
+            mbar_init(full + s, F_PWARPS);   // both producers stage half of every slot
+            mbar_init(vfull + s, F_HALVES);  // the two eval warps of the slot
+            mbar_init(empty + s, F_CWARPS + F_HWARPS + F_EWARPS);  // EVERY consumer warp, every slot
         }
         mbar_fence_init();
     }
     __syncthreads();
+    // Ring protocol.  Every warp of a role visits every slot in order and arrives on `empty` for
+    // every slot, whether or not it has work in it, and both producers wait on `empty` for every
+    // slot.  A parity wait is only sound while the waiter is less than one phase away from the
+    // barrier; with this rule no barrier can complete a phase that one of its waiters has not
+    // observed the previous phase of, for any stage count.
 
     if (warp >= F_PRODUCER && warp < F_PRODUCER + F_PWARPS) {
-        // ------------------------------ producer ------------------------------
-        // Row ids are fetched F_PF slots ahead (a register ring), so the global-load latency of the
-        // list never sits between "slot free" and "copy issued".  y is not loaded here: the staged
-        // width covers the response column and the eval warps read it from shared memory.
+        // ------------------------------ producers ------------------------------
+        // Producer pw stages rows [F_PSHARE pw, F_PSHARE (pw + 1)) of every slot, one row per lane.
         const int pw = warp - F_PRODUCER;
+        const int myrow = F_PSHARE * pw + lane;  // meaningful for lane < F_PSHARE
         if (a.rows == nullptr && a.ld == (long long)pitch) {
             // Contiguous rows whose pitch in HBM equals the slot pitch: the whole slot is ONE bulk
-            // copy (two when it straddles the held-out hole).  The TMA unit serves small copies at
-            // ~140 cycles each, so per-row copies cap at ~4.2 TB/s chip-wide; slot-sized ones do not.
-            for (int it = pw; it < nit; it += F_PWARPS) {
+            // copy (two when it straddles the held-out hole), issued by producer 0.  The TMA unit
+            // serves small copies at ~140 cycles each, so per-row copies cap at ~4.2 TB/s chip-wide;
+            // slot-sized ones do not.
+            for (int it = 0; it < nit; ++it) {
                 const int s = it % stages;
                 const uint32_t ph = (uint32_t)(it / stages) & 1u;
                 const long long t0 = c_begin + (long long)it * F_ROWS;
                 const int cnt = (int)((c_end - t0) < F_ROWS ? (c_end - t0) : F_ROWS);
                 wait_w(empty + s, ph ^ 1u, a, 1, it, s);
-                TRACE(0, it);  // producer: slot free
+                if (pw == 0) TRACE(0, it);  // producer: slot free
                 double *dst0 = sx + stage_doubles * s;
-                if (lane < F_ROWS) {
-                    sv[s * F_ROWS + lane] = lane < cnt ? 1.0 : 0.0;
-                    if (lane >= cnt)
-                        for (int c = 0; c < ncols; ++c) dst0[(size_t)lane * pitch + c] = 0.0;
+                if (lane < F_PSHARE) {
+                    sv[s * F_ROWS + myrow] = myrow < cnt ? 1.0 : 0.0;
+                    if (myrow >= cnt)
+                        for (int c = 0; c < ncols; ++c) dst0[(size_t)myrow * pitch + c] = 0.0;
                 }
                 __syncwarp();
                 if (lane == 0) {
-                    // rows t0 .. t0+cnt-1; positions >= hole_begin are shifted by hole_len
-                    long long n1 = a.hole_begin - t0;
-                    if (n1 < 0) n1 = 0;
-                    if (n1 > cnt) n1 = cnt;
-                    const long long n2 = cnt - n1;
-                    const uint32_t rowb = (uint32_t)pitch * 8u;
-                    mbar_arrive_expect_tx(full + s, rowb * (uint32_t)cnt);
-                    if (n1 > 0) bulk_g2s(dst0, a.X + (size_t)t0 * (size_t)a.ld, rowb * (uint32_t)n1, full + s);
-                    if (n2 > 0)
-                        bulk_g2s(dst0 + (size_t)n1 * pitch, a.X + (size_t)(t0 + n1 + a.hole_len) * (size_t)a.ld,
-                                 rowb * (uint32_t)n2, full + s);
+                    if (pw == 0) {
+                        // rows t0 .. t0+cnt-1; positions >= hole_begin are shifted by hole_len
+                        long long n1 = a.hole_begin - t0;
+                        if (n1 < 0) n1 = 0;
+                        if (n1 > cnt) n1 = cnt;
+                        const long long n2 = cnt - n1;
+                        const uint32_t rowb = (uint32_t)pitch * 8u;
+                        mbar_arrive_expect_tx(full + s, rowb * (uint32_t)cnt);
+                        if (n1 > 0) bulk_g2s(dst0, a.X + (size_t)t0 * (size_t)a.ld, rowb * (uint32_t)n1, full + s);
+                        if (n2 > 0)
+                            bulk_g2s(dst0 + (size_t)n1 * pitch, a.X + (size_t)(t0 + n1 + a.hole_len) * (size_t)a.ld,
+                                     rowb * (uint32_t)n2, full + s);
+                    } else {
+                        mbar_arrive(full + s);  // this producer's validity flags are in place
+                    }
                 }
                 __syncwarp();
             }
         } else {
-        constexpr int F_PF = 4;
-        auto fetch = [&](int it, long long &r) -> bool {
-            const long long t = c_begin + (long long)it * F_ROWS + lane;
-            if (lane >= F_ROWS || it >= nit || t >= c_end) return false;
-            const long long tp = t + (t >= a.hole_begin ? a.hole_len : 0);
-            r = a.rows ? (long long)__ldg(a.rows + tp) : tp;
-            return true;
-        };
-        long long ring_r[F_PF];
-        bool ring_ok[F_PF];
-#pragma unroll
-        for (int d = 0; d < F_PF; ++d) {
-            ring_r[d] = 0;
-            ring_ok[d] = fetch(pw + d * F_PWARPS, ring_r[d]);
-        }
-        for (int it0 = pw; it0 < nit; it0 += F_PF * F_PWARPS) {
+            // Row ids are fetched F_PF slots ahead (a register ring), so the global-load latency of
+            // the list never sits between "slot free" and "copy issued".
+            constexpr int F_PF = 4;
+            auto fetch = [&](int it, long long &r) -> bool {
+                const long long t = c_begin + (long long)it * F_ROWS + myrow;
+                if (lane >= F_PSHARE || it >= nit || t >= c_end) return false;
+                const long long tp = t + (t >= a.hole_begin ? a.hole_len : 0);
+                r = a.rows ? (long long)__ldg(a.rows + tp) : tp;
+                return true;
+            };
+            long long ring_r[F_PF];
+            bool ring_ok[F_PF];
 #pragma unroll
             for (int d = 0; d < F_PF; ++d) {
-                const int it = it0 + d * F_PWARPS;
-                if (it >= nit) break;
-                const long long cur_r = ring_r[d];
-                const bool cur_ok = ring_ok[d];
-                ring_ok[d] = fetch(it + F_PF * F_PWARPS, ring_r[d]);
-                const int s = it % stages;
-                const uint32_t ph = (uint32_t)(it / stages) & 1u;
-                wait_w(empty + s, ph ^ 1u, a, 2, it, s);
-                double *dst = sx + stage_doubles * s + (size_t)lane * pitch;
-                if (lane < F_ROWS) {
-                    sv[s * F_ROWS + lane] = cur_ok ? 1.0 : 0.0;
-                    if (!cur_ok)
-                        for (int c = 0; c < ncols; ++c) dst[c] = 0.0;
+                ring_r[d] = 0;
+                ring_ok[d] = fetch(d, ring_r[d]);
+            }
+            for (int it0 = 0; it0 < nit; it0 += F_PF) {
+#pragma unroll
+                for (int d = 0; d < F_PF; ++d) {
+                    const int it = it0 + d;
+                    if (it >= nit) break;
+                    const long long cur_r = ring_r[d];
+                    const bool cur_ok = ring_ok[d];
+                    ring_ok[d] = fetch(it + F_PF, ring_r[d]);
+                    const int s = it % stages;
+                    const uint32_t ph = (uint32_t)(it / stages) & 1u;
+                    wait_w(empty + s, ph ^ 1u, a, 2, it, s);
+                    if (pw == 0) TRACE(0, it);
+                    double *dst = sx + stage_doubles * s + (size_t)myrow * pitch;
+                    if (lane < F_PSHARE) {
+                        sv[s * F_ROWS + myrow] = cur_ok ? 1.0 : 0.0;
+                        if (!cur_ok)
+                            for (int c = 0; c < ncols; ++c) dst[c] = 0.0;
+                    }
+                    const unsigned vmask = __ballot_sync(0xffffffffu, cur_ok);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_expect_tx(full + s, row_bytes * (uint32_t)__popc(vmask));
+                    __syncwarp();
+                    if (cur_ok) bulk_g2s(dst, a.X + (size_t)cur_r * (size_t)a.ld, row_bytes, full + s);
                 }
-                const unsigned vmask = __ballot_sync(0xffffffffu, cur_ok);
-                __syncwarp();
-                if (lane == 0) mbar_arrive_expect_tx(full + s, row_bytes * (uint32_t)__popc(vmask));
-                __syncwarp();
-                if (cur_ok) bulk_g2s(dst, a.X + (size_t)cur_r * (size_t)a.ld, row_bytes, full + s);
             }
         }
-        }
-    } else if (warp >= F_PRODUCER + F_PWARPS) {
+    } else if (warp >= F_EVAL) {
         // ------------------------------ evaluation ------------------------------
-        const int e = warp - (F_PRODUCER + F_PWARPS);
+        // Eval warp e refreshes rows [16 half, 16 half + 16) of the slots whose turn it is.
+        const int e = warp - F_EVAL;
+        const int half = e % F_HALVES, turn = e / F_HALVES;
         const bool lead = (blockIdx.x == 0);
         const int ni = a.ni;
         double beta[2 * ITER];
@@ -278,16 +309,20 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
         const double a0 = a.coef[ni], w = a.w;
         const double pmin = GLM_PMIN, fmax_ = log(1.0 / pmin - 1.0), fmin_ = -fmax_;
         double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0;
-        const int rr = lane >> 1;  // the row of the slot this lane finishes
-        for (int it = e; it < nit; it += F_EWARPS) {
+        const int rr = F_HALF * half + (lane >> 1);  // the row of the slot this lane finishes
+        for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
             wait_w(full + s, ph, a, 3, it, s);
-            TRACE(1, it);  // eval: rows landed
-            const double *base = sx + stage_doubles * s;
-            double part[F_ROWS];
+            if ((it % F_TURNS) != turn) {  // not this warp's slot: release it at once
+                if (lane == 0) mbar_arrive(empty + s);
+                continue;
+            }
+            if (half == 0) TRACE(1, it);  // eval: rows landed
+            const double *base = sx + stage_doubles * s + (size_t)(F_HALF * half) * pitch;
+            double part[F_HALF];
 #pragma unroll
-            for (int q = 0; q < F_ROWS; ++q) {
+            for (int q = 0; q < F_HALF; ++q) {
                 const double *rowp = base + (size_t)q * pitch;
                 double dot = 0.0;
 #pragma unroll
@@ -302,16 +337,16 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
             }
             // reduce-scatter the 16 partial dots over the 32 lanes: lane l ends with row l >> 1
 #pragma unroll
-            for (int half = 8, off = 16; half >= 1; half >>= 1, off >>= 1) {
+            for (int hf = 8, off = 16; hf >= 1; hf >>= 1, off >>= 1) {
                 const bool up = (lane & off) != 0;
 #pragma unroll
-                for (int k = 0; k < half; ++k) {
-                    const double send = up ? part[k] : part[k + half], keep = up ? part[k + half] : part[k];
+                for (int k = 0; k < hf; ++k) {
+                    const double send = up ? part[k] : part[k + hf], keep = up ? part[k + hf] : part[k];
                     part[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
                 }
             }
             part[0] += __shfl_xor_sync(0xffffffffu, part[0], 1);
-            const double valid = sv[s * F_ROWS + rr], yi = base[(size_t)rr * pitch + a.iy];
+            const double valid = sv[s * F_ROWS + rr], yi = sx[stage_doubles * s + (size_t)rr * pitch + a.iy];
             const double fi = a0 + part[0];
             double q;
             if (fi < fmin_)
@@ -327,7 +362,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 sy[s * F_ROWS + rr] = ri;
             }
             __syncwarp();
-            TRACE(2, it);  // eval: v, r ready
+            if (half == 0) TRACE(2, it);  // eval: v, r ready
             if (lane == 0) {
                 mbar_arrive(vfull + s);  // MMA and helper warps may start on this slot
                 mbar_arrive(empty + s);  // ... and this warp is done with its staged rows
@@ -357,9 +392,10 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 ep[3 * ni + 2] = s_dev;
             }
         }
-    } else if (warp >= F_CWARPS) {
+    } else if (warp >= F_HELPER) {
         // ------------------------------ helpers: X^T r, X^T v (and sum v x^2 on the first step) -----
-        const int h = warp - F_CWARPS;
+        // Helper h owns rows [F_HSHARE h, F_HSHARE (h + 1)) of every slot.
+        const int h = warp - F_HELPER;
         const bool lead = (blockIdx.x == 0);
         const int ni = a.ni;
         double gr[2 * ITER], hx[2 * ITER], hxx[INIT ? 2 * ITER : 1];
@@ -368,18 +404,18 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
             gr[2 * i] = gr[2 * i + 1] = hx[2 * i] = hx[2 * i + 1] = 0.0;
             if (INIT) hxx[2 * i] = hxx[2 * i + 1] = 0.0;
         }
-        for (int it = h; it < nit; it += F_HWARPS) {
+        for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
             wait_w(full + s, ph, a, 4, it, s);
             if (lead) {
                 wait_w(vfull + s, ph, a, 5, it, s);
-                TRACE(3, it);  // helper: start
-                const double *base = sx + stage_doubles * s;
+                if (h == 0) TRACE(3, it);  // helper: start
+                const double *base = sx + stage_doubles * s + (size_t)(F_HSHARE * h) * pitch;
 #pragma unroll 4
-                for (int q2 = 0; q2 < F_ROWS; ++q2) {
-                    const double vj = sv[s * F_ROWS + q2];
-                    const double rj = sy[s * F_ROWS + q2];
+                for (int q2 = 0; q2 < F_HSHARE; ++q2) {
+                    const double vj = sv[s * F_ROWS + F_HSHARE * h + q2];
+                    const double rj = sy[s * F_ROWS + F_HSHARE * h + q2];
                     const double *rowp = base + (size_t)q2 * pitch;
 #pragma unroll
                     for (int i = 0; i < ITER; ++i) {
@@ -399,7 +435,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 }
             }
             __syncwarp();
-            TRACE(4, it);  // helper: done
+            if (h == 0) TRACE(4, it);  // helper: done
             if (lane == 0) mbar_arrive(empty + s);
         }
         if (lead) {
@@ -523,8 +559,7 @@ struct StepPlan {
     int ngroups[F_MAX_NTR + 1];
     int max_tiles[F_MAX_NTR + 1];
     std::vector<uint2> tab;
-    int min_tiles = 16;  // measured on B200: spreading a narrow list over more MMA warps is slower (the warps
-                         // contend for shared-memory reads), so rows are packed block-like; ATE_PLAN_MINT overrides
+    int min_tiles = 1;   // ATE_PLAN_MINT: lower bound on the busiest warp's tile count (experiments)
     StepPlan() : tab((size_t)(F_MAX_NTR + 1) * F_PLAN_W, make_uint2(0u, 0u)) {
         if (const char *e = getenv("ATE_PLAN_MINT")) min_tiles = atoi(e);
         ngroups[0] = 1;
@@ -562,8 +597,13 @@ struct StepPlan {
     }
     void build(int ntr) {
         const int total = ntr * (ntr + 1) / 2;
-        for (int g = 1; 8 * g <= F_PLAN_W; ++g) {
-            const int W = 8 * g;
+        // g groups of 8 warp slots.  First try to get by with FOUR warps per group -- warps 0-3 sit on
+        // the four SM sub-partitions, and one warp per sub-partition already saturates its DMMA pipe
+        // (16.7 cycles per DMMA.8x8x4 alone, 32 with two warps: tools/microbench/dmma_shapes.cu) --
+        // then with all eight.
+        for (int pass = 0; pass < 2 * (F_PLAN_W / 8); ++pass) {
+            const int g = pass / 2 + 1, per = (pass % 2 == 0) ? 4 : 8;
+            const int W = per * g;
             int T0 = (total + W - 1) / W;
             if (T0 < min_tiles) T0 = min_tiles;
             for (int T = T0; T <= 16; ++T) {
@@ -571,7 +611,8 @@ struct StepPlan {
                 if (pack(ntr, T, nullptr) <= W) {
                     std::vector<uint2> d;
                     pack(ntr, T, &d);
-                    for (size_t k = 0; k < d.size(); ++k) tab[(size_t)ntr * F_PLAN_W + k] = d[k];
+                    for (size_t k = 0; k < d.size(); ++k)
+                        tab[(size_t)ntr * F_PLAN_W + 8 * (k / per) + (k % per)] = d[k];
                     ngroups[ntr] = g;
                     max_tiles[ntr] = T;
                     return;
