@@ -8,12 +8,12 @@
 // HBM-bound kernel (algorithmic bytes: nrows * (ncols + 1) * 8) and the coordinate descent runs
 // on the p x p result (path_binom.cu).
 //
-// CTA = 8 MMA warps + 2 helper warps + 2 producer warps + 4 evaluation warps, one CTA per SM, around
-// a ring of 32-row slots in shared memory (three at the C1 width of 264 staged columns).  Measured
-// with the per-slot trace (-DATE_STEP_TRACE): every role pays ~1-2 thousand cycles per slot that do
-// not depend on the slot's size (barrier round trips, operand-load latency at the head of the MMA
-// chain), so 16-row slots ran at 2600 cycles per slot whichever way the work was dealt; 32-row
-// slots halve that overhead per row.
+// CTA = 8 MMA warps + 2 producer warps + 2 helper warps + 4 evaluation warps, one CTA per SM, around
+// a ring of 32-row slots in shared memory (three at the C1 width of 264 staged columns).  No pipe
+// bounds this kernel (ncu: shared-memory pipe 50-66 %, DMMA 34-65 %, issue slots 37 %): the per-slot
+// trace (-DATE_STEP_TRACE, tools/step_trace.py) shows the serial life of a slot -- fill, evaluate,
+// consume -- pacing the ring, at ~2500 cycles per 16 rows where HBM speed would be 1500.  16-row
+// slots with six in the ring measure the same; see DESIGN.md section 5 for what was tried.
 //   producers: producer pw stages rows [16 pw, 16 pw + 16) of every slot with one-dimensional TMA
 //              bulk copies (one per lane; ONE copy for the whole slot when the rows are contiguous
 //              at the slot's pitch) into an mbarrier ring, plus a validity flag per row.
