@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libate_b200.so")
+# ATE_B200_LIB: load another build of the same library (same-box A/B timing of kernel variants)
+SO_PATH = os.environ.get("ATE_B200_LIB") or os.path.join(_HERE, "libate_b200.so")
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)

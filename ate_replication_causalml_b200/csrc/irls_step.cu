@@ -49,9 +49,9 @@ using namespace atk;
 #ifndef ATE_STEP_ROWS
 #define ATE_STEP_ROWS 32
 #endif
-constexpr int F_ROWS = ATE_STEP_ROWS;  // rows per slot (16 or 32)
+constexpr int F_ROWS = ATE_STEP_ROWS;  // rows per slot (16, 24 or 32)
 constexpr int F_HALF = 16;             // an eval warp refreshes 16 rows at a time (its reduce-scatter is 16 wide)
-constexpr int F_HALVES = F_ROWS / F_HALF;
+constexpr int F_HALVES = (F_ROWS + F_HALF - 1) / F_HALF;  // the last one may be short (24-row slots: 16 + 8)
 constexpr int F_CWARPS = 8;   // MMA warps;  8 + 2 + 2 + 4 = 16 warps: 128 registers per thread
 constexpr int F_HWARPS = 2;   // helper warps (X^T r, X^T v); each owns an equal share of the rows of every slot
 constexpr int F_EWARPS = 4;   // evaluation warps, taking turns on the slots (see F_TURNS)
@@ -72,7 +72,7 @@ constexpr size_t F_SMEM_LIMIT = 227 * 1024;
 constexpr int F_PSHARE = F_ROWS / F_PWARPS;  // rows of every slot staged by one producer (one per lane)
 constexpr int F_HSHARE = F_ROWS / F_HWARPS;  // rows of every slot accumulated by one helper
 constexpr int F_TURNS = F_EWARPS / F_HALVES; // eval warp e refreshes half e % F_HALVES of the slots with it % F_TURNS == e / F_HALVES
-static_assert(F_HALF == 16 && (F_ROWS == 16 || F_ROWS == 32) && F_EWARPS % F_HALVES == 0 && F_ROWS % F_PWARPS == 0 &&
+static_assert(F_HALF == 16 && (F_ROWS == 16 || F_ROWS == 24 || F_ROWS == 32) && F_EWARPS % F_HALVES == 0 && F_ROWS % F_PWARPS == 0 &&
                   F_ROWS % F_HWARPS == 0,
               "slot geometry");
 
@@ -323,7 +323,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
             double part[F_HALF];
 #pragma unroll
             for (int q = 0; q < F_HALF; ++q) {
-                const double *rowp = base + (size_t)q * pitch;
+                // a short last half re-reads its last row for the missing ones; those lanes are masked below
+                const int qq = (F_ROWS % F_HALF != 0 && F_HALF * half + q >= F_ROWS) ? F_ROWS - 1 - F_HALF * half : q;
+                const double *rowp = base + (size_t)qq * pitch;
                 double dot = 0.0;
 #pragma unroll
                 for (int i = 0; i < ITER; ++i) {
@@ -346,7 +348,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 }
             }
             part[0] += __shfl_xor_sync(0xffffffffu, part[0], 1);
-            const double valid = sv[s * F_ROWS + rr], yi = sx[stage_doubles * s + (size_t)rr * pitch + a.iy];
+            const bool inslot = rr < F_ROWS;
+            const int rc = inslot ? rr : F_ROWS - 1;
+            const double valid = inslot ? sv[s * F_ROWS + rc] : 0.0, yi = sx[stage_doubles * s + (size_t)rc * pitch + a.iy];
             const double fi = a0 + part[0];
             double q;
             if (fi < fmin_)
@@ -357,7 +361,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) irls_step_kernel(const StepArgs 
                 q = 1.0 / (1.0 + exp(-fi));
             const double vi = w * q * (1.0 - q) * valid, ri = w * (yi - q) * valid;
             __syncwarp();  // every lane has read the validity flag before it is overwritten
-            if ((lane & 1) == 0) {
+            if ((lane & 1) == 0 && inslot) {
                 sv[s * F_ROWS + rr] = vi;
                 sy[s * F_ROWS + rr] = ri;
             }
