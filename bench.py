@@ -162,17 +162,18 @@ def run_reference(args, rank):
         return
     t0 = time.perf_counter()
     vals = []
-    for _ in range(max(1, args.warmup) if args.warmup < 1 else 0):
-        pass
     steps = max(1, args.steps)
     desc = ""
     cores = 1
+    warm = 1 if args.warmup >= 1 else 0  # one untimed sample pages the oracle library and its threads in
+    for _ in range(warm):
+        cpu_sample(args, args.cpu_sample_n)
     for _ in range(steps):
         dt, fps, cores, desc = cpu_sample(args, args.cpu_sample_n)
         vals.append((dt, fps))
     fps = float(np.mean([v[1] for v in vals]))
     ms = 1e3 / fps
-    line = dict(metric=METRIC, value=fps, unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=0,
+    line = dict(metric=METRIC, value=fps, unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warm,
                 ms_per_step=ms, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f64",
                 data="synthetic", impl="reference", config=workload(args),
                 cpu_baseline=dict(value=fps, unit=UNIT, cores=cores, kind="port",
@@ -218,6 +219,11 @@ def main():
         raise SystemExit("bench.py: no CUDA device (the engine has no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # stdout carries exactly ONE JSON line (rank 0).  NCCL prints its version banner on fd 1 when the
+    # box exports NCCL_DEBUG=VERSION, so everything up to the final print goes to stderr instead.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -304,10 +310,19 @@ def main():
         except Exception:
             pass
         achieved = prof["gram_bytes"] / gl / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        # DRAM bytes of one launch from the committed ncu --set full capture (a smaller launch than
+        # this run's: the ratio to its algorithmic bytes is what carries over)
+        traffic, traffic_capture = None, None
+        try:
+            traffic_capture = json.load(open(os.path.join(ROOT, "profiles", "r01b_irls_step_traffic.json")))
+            traffic = traffic_capture["dram_bytes_per_launch"]
+        except Exception:
+            pass
         tf = prof["gram_flops"] / gl / (avg_ms * 1e-3) / 1e12 if avg_ms > 0 else 0.0
         roof = dict(bound="hbm", kernel="irls_step_kernel (fused IRLS step: eta/q/v/r, X^T r, X^T v and the "
                                         "strong-set Gram X_S^T V X_S on DMMA from one pass over the rows)",
-                    achieved=achieved, peak=hbm_peak, unit="GB/s", frac=achieved / hbm_peak, traffic=None,
+                    achieved=achieved, peak=hbm_peak, unit="GB/s", frac=achieved / hbm_peak, traffic=traffic,
+                    traffic_capture=traffic_capture,
                     launches=prof["gram_launches"], avg_launch_ms=avg_ms, share_of_step=prof["gram_ms"] / ms_total,
                     algorithmic="nrows*(p+2)*8 bytes per launch (each staged row read once, v written once)",
                     peak_source=peak_src,
@@ -335,7 +350,8 @@ def main():
                                 strong_frac2=last.get("strong_frac2"),
                                 stage_ms={k: last.get(k) for k in ("ms_design", "ms_outcome", "ms_propensity",
                                                                     "ms_score", "ms_bootstrap")}))
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     eng.close()
     if world > 1:
         dist.destroy_process_group()
