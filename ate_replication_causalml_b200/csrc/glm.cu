@@ -119,7 +119,7 @@ extern "C" int ate_glm_binomial(ate_ctx *ctx, long long n, int p, const double *
                                 double epsilon, double *coef, double *deviance, int *iters, int *converged) {
     if (!ctx) return -1;
     if (!x || !y || !coef || n < 2 || p < 0) return ate_fail(ctx, -1, "ate_glm_binomial: bad arguments");
-    if (p + 3 > 416) return ate_fail(ctx, -1, "ate_glm_binomial: p = %d exceeds the full-row Gram kernel", p);
+    if (p + 3 > 2048) return ate_fail(ctx, -1, "ate_glm_binomial: p = %d is beyond the host solve this entry point uses", p);
     ATE_CUDA(ctx, cudaSetDevice(ctx->device));
     if (maxit <= 0) maxit = 25;
     if (!(epsilon > 0)) epsilon = 1e-8;

@@ -33,6 +33,7 @@ constexpr int G_CWARPS = 12;  // consumer (MMA) warps per CTA
 constexpr int G_THREADS = (G_CWARPS + 1) * 32;
 constexpr int G_PAD = 4;      // doubles of padding per staged row
 constexpr int G_MAX_STAGES = 4;
+constexpr int G_PANEL = 96;   // column panel of the wide-design path: 3 x 3 blocks per pair = 9 of the 12 MMA warps
 constexpr size_t G_SMEM_LIMIT = 227 * 1024;
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -85,7 +86,10 @@ __global__ void __launch_bounds__(G_THREADS, 1)
 gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const int32_t *__restrict__ rows,
                  long long row_begin, long long nrows, long long hole_begin, long long hole_len,
                  long long rows_per_chunk, const double *__restrict__ v, int nblk, int stages,
-                 const int *__restrict__ colidx, double *__restrict__ partials) {
+                 const int *__restrict__ colidx, double *__restrict__ partials, int wA, long long offB) {
+    // Panel-pair mode (wA > 0; designs too wide to stage a whole row): a staged row is
+    // [X[r, 0 : wA) | X[r, offB : offB + ncols - wA)] (two bulk copies) and the blocks are the
+    // rectangle (second panel) x (first panel), block q = (q / (wA/32), q % (wA/32)).
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int pitch = ncols + G_PAD;                       // doubles
     const size_t stage_doubles = (size_t)G_ROWS * pitch;
@@ -143,7 +147,15 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
             __syncwarp();
             if (lane == 0) mbar_arrive_expect_tx(full + s, row_bytes * (uint32_t)__popc(vmask));
             __syncwarp();
-            if (cur_ok) bulk_g2s(dst, X + (size_t)cur_r * (size_t)ld, row_bytes, full + s);
+            if (cur_ok) {
+                const double *src = X + (size_t)cur_r * (size_t)ld;
+                if (wA > 0) {
+                    bulk_g2s(dst, src, (uint32_t)wA * 8u, full + s);
+                    bulk_g2s(dst + wA, src + offB, row_bytes - (uint32_t)wA * 8u, full + s);
+                } else {
+                    bulk_g2s(dst, src, row_bytes, full + s);
+                }
+            }
             cur_ok = nxt_ok;
             cur_r = nxt_r;
             cur_v = nxt_v;
@@ -153,7 +165,15 @@ gram_dmma_kernel(const double *__restrict__ X, long long ld, int ncols, const in
         const int q = blockIdx.x * G_CWARPS + warp;
         const bool active = q < nblk;
         int bi = 0, bj = 0;
-        if (active) block_coords(q, bi, bj);
+        if (active) {
+            if (wA > 0) {
+                const int nbA = wA >> 5;
+                bi = nbA + q / nbA;  // staged columns of the second panel start at wA
+                bj = q % nbA;
+            } else {
+                block_coords(q, bi, bj);
+            }
+        }
         const bool diag = (bi == bj);
         double acc[4][4][2];
 #pragma unroll
@@ -240,6 +260,23 @@ gram_fold_kernel(const double *__restrict__ partials, int nchunks, int nblk, int
     }
 }
 
+// fold for the panel-pair mode: block q is (q / nbA, q % nbA) of the rectangle G[rowoff.., coloff..]
+__global__ void __launch_bounds__(256)
+gram_fold_rect_kernel(const double *__restrict__ partials, int nchunks, int nblk, int nbA, int rowoff, int coloff, int p,
+                      int ldg, double *__restrict__ G) {
+    const int q = blockIdx.x;
+    const int e = blockIdx.y * 256 + threadIdx.x;
+    const double *src = partials + (size_t)q * 1024 + e;
+    const size_t cstride = (size_t)nblk * 1024;
+    double s = 0.0;
+    for (int c = 0; c < nchunks; ++c) s += __ldg(src + (size_t)c * cstride);
+    const int r = rowoff + (q / nbA) * 32 + (e >> 5), col = coloff + (q % nbA) * 32 + (e & 31);
+    if (r < p && col < p) {
+        G[(size_t)r * ldg + col] = s;
+        G[(size_t)col * ldg + r] = s;
+    }
+}
+
 }  // namespace
 
 int ate_i_gram_fold(ate_ctx *ctx, const double *partials, int nchunks, int nblk, int p, int ldg, double *G) {
@@ -273,8 +310,79 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
     const size_t stage_bytes = sizeof(double) * (size_t)G_ROWS * (ncols + G_PAD);
     int stages = (int)((G_SMEM_LIMIT - 1024) / (stage_bytes + G_ROWS * sizeof(double)));
     if (stages > G_MAX_STAGES) stages = G_MAX_STAGES;
-    if (stages < 2)
-        return ate_fail(ctx, -1, "gram: p = %d exceeds the full-row kernel (needs the panel variant)", p);
+    if (stages < 2) {
+        // A row of this design does not fit the staging ring: cut the columns into panels of
+        // G_PANEL and run one launch per panel (triangular) and per panel pair (rectangular).  Every
+        // 32x32 block is still computed exactly once; rows are re-read once per panel pair, which at
+        // these widths (>= 2 * 96^2 flop per 1.5 KB staged) stays far below the DMMA time.
+        if (colidx) return ate_fail(ctx, -1, "gram: a %d-column list does not fit the full-row kernel", ncload);
+        if (pp > ld) return ate_fail(ctx, -1, "gram: ld (%lld) < padded column count (%d)", ld, pp);
+        static bool attr_set_w = false;
+        if (!attr_set_w) {
+            ATE_CUDA(ctx, cudaFuncSetAttribute(gram_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_LIMIT));
+            attr_set_w = true;
+        }
+        auto launch = [&](const double *Xb, int nc, int nblk_l, int wA, long long offB, double **scr_out, int *nchunks_out,
+                          double flops) -> int {
+            const size_t sb = sizeof(double) * (size_t)G_ROWS * (nc + G_PAD);
+            int st = (int)((G_SMEM_LIMIT - 1024) / (sb + G_ROWS * sizeof(double)));
+            if (st > G_MAX_STAGES) st = G_MAX_STAGES;
+            const size_t sm = st * (sb + G_ROWS * sizeof(double)) + 2 * st * sizeof(uint64_t);
+            const int ngr = (nblk_l + G_CWARPS - 1) / G_CWARPS;
+            int nch = ctx->num_sms / ngr;
+            if (nch < 1) nch = 1;
+            long long mc = (nrows + 4 * G_ROWS - 1) / (4 * G_ROWS);
+            if (mc < 1) mc = 1;
+            if (nch > mc) nch = (int)mc;
+            long long rpc_l = (nrows + nch - 1) / nch;
+            rpc_l = (rpc_l + G_ROWS - 1) / G_ROWS * G_ROWS;
+            if (rpc_l < G_ROWS) rpc_l = G_ROWS;
+            nch = (int)((nrows + rpc_l - 1) / rpc_l);
+            if (nch < 1) nch = 1;
+            void *scr_l = nullptr;
+            ATE_TRY(ate_gram_scratch(ctx, sizeof(double) * 1024 * (size_t)nblk_l * nch, &scr_l));
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            if (ctx->profile) {
+                ATE_CUDA(ctx, cudaEventCreate(&e0));
+                ATE_CUDA(ctx, cudaEventCreate(&e1));
+                ATE_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+            }
+            gram_dmma_kernel<<<dim3(ngr, nch), G_THREADS, sm, ctx->stream>>>(Xb, ld, nc, rows, row_begin, nrows, hole_begin,
+                                                                            hole_len, rpc_l, v, nblk_l, st, nullptr,
+                                                                            (double *)scr_l, wA, offB);
+            ATE_LAUNCHED(ctx);
+            if (ctx->profile) {
+                ATE_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+                ctx->prof_events.emplace_back(e0, e1);
+                ctx->prof_shape.emplace_back(-nc, nrows);
+                ctx->prof_launches++;
+                ctx->prof_flops += flops;
+                ctx->prof_bytes += (double)nrows * (nc + 1.0) * 8.0;
+            }
+            *scr_out = (double *)scr_l;
+            *nchunks_out = nch;
+            return 0;
+        };
+        const int npan = (pp + G_PANEL - 1) / G_PANEL;
+        for (int I = 0; I < npan; ++I) {
+            const int cI = I * G_PANEL, wI = (pp - cI < G_PANEL) ? pp - cI : G_PANEL, nbI = wI / 32;
+            double *scr_l = nullptr;
+            int nch = 0;
+            const int pI = (p - cI < wI) ? p - cI : wI;  // real columns of this panel
+            ATE_TRY(launch(X + cI, wI, nbI * (nbI + 1) / 2, 0, 0, &scr_l, &nch, (double)nrows * pI * (pI + 1.0)));
+            gram_fold_kernel<<<dim3(nbI * (nbI + 1) / 2, 4), 256, 0, ctx->stream>>>(scr_l, nch, nbI * (nbI + 1) / 2, pI, p,
+                                                                                   G + (size_t)cI * p + cI);
+            ATE_LAUNCHED(ctx);
+            for (int J = 0; J < I; ++J) {
+                const int cJ = J * G_PANEL, nbJ = G_PANEL / 32;
+                ATE_TRY(launch(X + cJ, G_PANEL + wI, nbI * nbJ, G_PANEL, (long long)(cI - cJ), &scr_l, &nch,
+                               2.0 * (double)nrows * pI * G_PANEL));
+                gram_fold_rect_kernel<<<dim3(nbI * nbJ, 4), 256, 0, ctx->stream>>>(scr_l, nch, nbI * nbJ, nbJ, cI, cJ, p, p, G);
+                ATE_LAUNCHED(ctx);
+            }
+        }
+        return 0;
+    }
     const size_t smem = stages * (stage_bytes + G_ROWS * sizeof(double)) + 2 * stages * sizeof(uint64_t);
     const int ngroups = (nblk + G_CWARPS - 1) / G_CWARPS;
     int nchunks = ctx->num_sms / ngroups;
@@ -301,7 +409,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
         ATE_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
     }
     gram_dmma_kernel<<<dim3(ngroups, nchunks), G_THREADS, smem, ctx->stream>>>(
-        X, ld, ncols, rows, row_begin, nrows, hole_begin, hole_len, rpc, v, nblk, stages, colidx, (double *)scr);
+        X, ld, ncols, rows, row_begin, nrows, hole_begin, hole_len, rpc, v, nblk, stages, colidx, (double *)scr, 0, 0);
     ATE_LAUNCHED(ctx);
     if (ctx->profile) {
         ATE_CUDA(ctx, cudaEventRecord(e1, ctx->stream));

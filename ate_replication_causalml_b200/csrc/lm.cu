@@ -117,7 +117,7 @@ extern "C" int ate_lm(ate_ctx *ctx, long long n, int p, const double *x, const d
                       long long *df_residual, double *resid) {
     if (!ctx) return -1;
     if ((!x && p > 0) || !y || !coef || n < 1 || p < 0) return ate_fail(ctx, -1, "ate_lm: bad arguments");
-    if (p + 2 > 416) return ate_fail(ctx, -1, "ate_lm: p = %d exceeds the full-row Gram kernel", p);
+    if (p + 2 > 2048) return ate_fail(ctx, -1, "ate_lm: p = %d is beyond the host factorisation this entry point uses", p);
     if (weights)
         for (long long i = 0; i < n; ++i)
             if (!(weights[i] >= 0.0)) return ate_fail(ctx, -1, "ate_lm: missing or negative weights not allowed");

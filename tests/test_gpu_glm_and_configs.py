@@ -226,3 +226,25 @@ def test_belloni_end_to_end(engine, oracle):
     assert row.attrs["fit"]["rank"] == o["rank"]
     o2 = oracle.lm(np.column_stack([x[:, cu - 1], d["w"]]), d["y"])
     assert abs(row["ATE"][0] - o2["coef"][-1]) <= 0.1 * o2["std_err"][-1]   # one marginal regressor more or less
+
+
+def test_wide_designs_beyond_one_staged_row(engine, oracle):
+    """BASELINE.json configs[3]/[4] are wider (p = 1024 / 512) than a row the staging ring holds; the
+    Gram then runs panel by panel.  Gaussian cv.glmnet (C3 is a 10-fold CV path) and lm at such widths
+    against the oracle, at an n the oracle finishes quickly."""
+    rng = np.random.default_rng(5)
+    n, p = 3000, 530
+    x = rng.standard_normal((n, p)) * rng.uniform(0.5, 2.0, p)
+    beta = np.zeros(p); beta[rng.choice(p, 12, replace=False)] = rng.uniform(-1, 1, 12)
+    y = x @ beta + rng.standard_normal(n)
+    fid = synth.fold_ids(n, 10, 7)
+    g = engine.cv_glmnet(x, y, "gaussian", foldid=fid, nlambda=40)
+    o = oracle.cv_glmnet(x, y, fid, "gaussian", nlambda=40)
+    assert g["lmu"] == o["lmu"] and g["idx_min"] == o["idx_min"] and g["idx_1se"] == o["idx_1se"]
+    assert np.abs(g["lambda_"] - o["lambda_"]).max() <= 1e-12 * o["lambda_"][0]
+    assert np.abs(g["beta"] - o["beta"]).max() <= 1e-8 and np.abs(g["cvm"] - o["cvm"]).max() <= 1e-9 * o["cvm"].max()
+    gl, ol = engine.lm(x[:, :450], y), oracle.lm(x[:, :450], y)
+    _lm_close(gl, ol, tol=1e-8)
+    from ate_replication_causalml_b200._lib import AteError
+    with pytest.raises(AteError, match="fit"):        # the binomial step still needs a whole row staged
+        engine.cv_glmnet(x, (y > 0).astype(float), "binomial", foldid=fid, nlambda=10)

@@ -175,7 +175,8 @@ def test_r_rng_bit_exact_with_oracle_and_known_answers(engine, oracle, golden):
 
 
 # ---------------------------------------------------------------- weighted Gram
-@pytest.mark.parametrize("n,p", [(1, 1), (31, 5), (1000, 40), (4097, 256), (3000, 70), (513, 288)])
+@pytest.mark.parametrize("n,p", [(1, 1), (31, 5), (1000, 40), (4097, 256), (3000, 70), (513, 288),
+                                 (2500, 417), (3000, 515), (1500, 1027)])   # the last three: panel-pair path
 def test_weighted_gram_matches_numpy(engine, n, p):
     rng = np.random.default_rng(n + p)
     x = rng.standard_normal((n, p))
