@@ -807,7 +807,9 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         g.list = Xp[p] ? nullptr : probs[p].d_list;
         g.nt = fit_nt[id]; g.hole_begin = fit_hb[id]; g.hole_len = fit_hl[id];
         g.ni = ni; g.iy = iy; g.ldh = ldh; g.ncs = ncs;
-        g.owned = (id < nlead || po.shard_count <= 1 || ((id - nlead) % po.shard_count) == po.shard_rank) ? 1 : 0;
+        // ranks sharing a fit deal BOTH the full-data fits and the cv-fold paths round-robin; the
+        // full-data results are exchanged between the two phases (below)
+        g.owned = (po.shard_count <= 1 || ((id < nlead ? id : id - nlead) % po.shard_count) == po.shard_rank) ? 1 : 0;
         g.vp = vp_host ? dvp.p : nullptr;
         g.nlam = nlam; g.thr = po.thr; g.maxit = po.maxit;
         g.v = dvr_p + vr_off[id];
@@ -905,6 +907,42 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             }
             if (timing) { const double t = tnow(); t_solve += t - t_mark; t_mark = t; }
             if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
+        }
+        if (phase == 0 && po.shard_count > 1 && nlead > 0) {
+            // Every full-data fit was solved by exactly one rank.  Its lambda sequence gates the
+            // cv-fold paths of ALL ranks and its path is the model that is returned, so each rank
+            // now receives the fits it did not solve: the records are zero-filled by non-owners and
+            // summed through the host all-reduce hook (x + 0 is exact: bit-identical to one GPU).
+            if (!ctx->allreduce) return ate_fail(ctx, -1, "cv_binomial: sharded fit but no all-reduce hook set");
+            const size_t rec = out_len + 4;  // path outputs, then lmu, nlp, jerr, dev0
+            std::vector<double> xb(rec * (size_t)nlead, 0.0), tmp(out_len);
+            std::vector<int> ti(SI_N);
+            for (int id = 0; id < nlead; ++id) {
+                if (!hf[id].owned) continue;
+                double *r = xb.data() + rec * (size_t)id;
+                ATE_CUDA(ctx, cudaMemcpyAsync(r, dout.p + out_len * id, sizeof(double) * out_len, cudaMemcpyDeviceToHost, ctx->stream));
+                ATE_CUDA(ctx, cudaMemcpyAsync(ti.data(), hf[id].st_i + si_scal, sizeof(int) * SI_N, cudaMemcpyDeviceToHost, ctx->stream));
+                ATE_CUDA(ctx, cudaMemcpyAsync(r + out_len + 3, hf[id].st_d + 7 * (size_t)ni + SD_DEV0, sizeof(double),
+                                              cudaMemcpyDeviceToHost, ctx->stream));
+                ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                r[out_len] = ti[SI_LMU];
+                r[out_len + 1] = ti[SI_NLP];
+                r[out_len + 2] = ti[SI_JERR];
+            }
+            if (ctx->allreduce(ctx->allreduce_user, xb.data(), (long long)xb.size()) != 0)
+                return ate_fail(ctx, -4, "cv_binomial: all-reduce hook failed");
+            for (int id = 0; id < nlead; ++id) {
+                if (hf[id].owned) continue;
+                const double *r = xb.data() + rec * (size_t)id;
+                ATE_CUDA(ctx, cudaMemcpyAsync(dout.p + out_len * id, r, sizeof(double) * out_len, cudaMemcpyHostToDevice, ctx->stream));
+                const int iv3[3] = {(int)r[out_len], (int)r[out_len + 1], (int)r[out_len + 2]};
+                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_i + si_scal + SI_LMU, &iv3[0], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_i + si_scal + SI_NLP, &iv3[1], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_i + si_scal + SI_JERR, &iv3[2], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_d + 7 * (size_t)ni + SD_DEV0, r + out_len + 3, sizeof(double),
+                                              cudaMemcpyHostToDevice, ctx->stream));
+                ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // iv3 and xb are host temporaries
+            }
         }
     }
 
