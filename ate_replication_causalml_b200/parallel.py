@@ -2,13 +2,13 @@
 
 One process per GPU (torchrun); every rank holds the full inputs (n = 1M x p0 = 16 doubles is
 128 MB) and builds its own design.  What is sharded:
-  * the cv-fold lambda paths of the propensity model (50 of the 55 path fits) -- dealt
-    round-robin over ranks inside the library; the held-out deviances of all folds meet
-    through ONE small host all-reduce (K * nfolds * nlambda doubles), after which every rank
-    selects the same lambda;
+  * all 55 lambda paths of the propensity model -- the 5 full-data fits, then the 50 cv-fold
+    paths, each set dealt round-robin over ranks inside the library; the full-data paths (1 MB)
+    and the held-out deviances of all folds (K * nfolds * nlambda doubles) meet through the host
+    all-reduce hook, after which every rank holds the same models and selects the same lambda;
   * the bootstrap replicates -- rank r draws replicates [r*B/N, (r+1)*B/N) with the Philox
     stream keyed by replicate id, so the union is identical to the 1-GPU run.
-The full-data fits (5 of 55) and the gaussian outcome model (a few Gram passes) are replicated.
+The gaussian outcome model (a few Gram passes) is replicated.
 """
 from __future__ import annotations
 

@@ -67,9 +67,10 @@ ATE_API int ate_profile_read(ate_ctx *ctx, double *gram_ms, long long *gram_laun
 
 /* Multi-GPU hook (no reference counterpart: the reference is single-threaded).  When one fit is
  * shared by several ranks (ate_crossfit_opts.shard_count > 1) the library calls `fn` to sum a
- * small HOST buffer of doubles over all ranks (held-out CV deviances of the cv-fold paths each
- * rank solved).  The R shim would bind this to ncclAllReduce / MPI_Allreduce; bench.py binds it
- * to torch.distributed.  Must return 0 on success. */
+ * small HOST buffer of doubles over all ranks (the paths of the full-data fits and the held-out
+ * CV deviances of the cv-fold paths each rank solved; non-owners contribute zeros).  The R shim
+ * would bind this to ncclAllReduce / MPI_Allreduce; bench.py binds it to torch.distributed.  Must
+ * return 0 on success. */
 typedef int (*ate_allreduce_fn)(void *user, double *host_buf, long long count);
 ATE_API int ate_ctx_set_allreduce(ate_ctx *ctx, ate_allreduce_fn fn, void *user);
 
@@ -209,7 +210,7 @@ typedef struct ate_crossfit_opts {
     int fold_end;       /*   0,0 = all); rows of other folds get NaN nuisances                */
     int skip_score;     /* 1: stop after the nuisances (multi-GPU drivers combine first)      */
     int shard_rank;     /* this process's rank and the number of ranks sharing ONE fit: the   */
-    int shard_count;    /*   cv-fold paths are dealt round-robin over ranks (0,0 = no sharding) */
+    int shard_count;    /*   propensity paths are dealt round-robin over ranks (0,0 = no sharding) */
 } ate_crossfit_opts;
 
 ATE_API void ate_crossfit_default_opts(ate_crossfit_opts *o);
