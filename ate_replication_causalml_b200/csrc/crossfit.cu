@@ -355,19 +355,47 @@ extern "C" int ate_crossfit_aipw(ate_ctx *ctx, const ate_crossfit_opts *opts, lo
     {
         std::vector<double> vp((size_t)p + 1, 1.0);
         vp[p] = 0.0;
-        std::vector<CvOut> outs;
-        ATE_TRY(ate_i_cv_gaussian(ctx, dX.p, ld, p + 1, p + 1, p + 2, vp.data(), po, prob_out, outs));
+        // Selected model of every fold: jerr, lmu, lambda, a0, beta[p + 1].  Ranks sharing the fit
+        // solve the folds round-robin and sum the zero-filled records through the all-reduce hook.
+        const size_t rec = (size_t)p + 5;
+        std::vector<double> sel(rec * (size_t)nk, 0.0);
+        const bool shared = o.shard_count > 1;
+        if (shared && !ctx->allreduce) return ate_fail(ctx, -1, "ate_crossfit_aipw: sharded fit but no all-reduce hook set");
+        std::vector<CvProblem> mine;
+        std::vector<int> mine_q;
+        for (int q = 0; q < nk; ++q)
+            if (!shared || q % o.shard_count == o.shard_rank) {
+                mine.push_back(prob_out[q]);
+                mine_q.push_back(q);
+            }
+        if (!mine.empty()) {
+            std::vector<CvOut> outs;
+            ATE_TRY(ate_i_cv_gaussian(ctx, dX.p, ld, p + 1, p + 1, p + 2, vp.data(), po, mine, outs));
+            for (size_t m = 0; m < mine.size(); ++m) {
+                const CvOut &c = outs[m];
+                double *r = sel.data() + rec * (size_t)mine_q[m];
+                r[0] = c.jerr;
+                r[1] = c.lmu;
+                if (c.lmu < 1) continue;
+                const int s = o.use_1se ? c.idx_1se : c.idx_min;
+                r[2] = c.lambda[s];
+                r[3] = c.a0[s];
+                for (int j = 0; j <= p; ++j) r[4 + j] = c.beta[(size_t)s * (p + 1) + j];
+            }
+        }
+        if (shared && ctx->allreduce(ctx->allreduce_user, sel.data(), (long long)sel.size()) != 0)
+            return ate_fail(ctx, -4, "ate_crossfit_aipw: all-reduce hook failed");
         for (int q = 0; q < nk; ++q) {
-            const CvOut &c = outs[q];
-            if (c.jerr > 0 || c.lmu < 1) return ate_fail(ctx, -3, "outcome fit of fold %d failed (jerr %d)", kb + q, c.jerr);
-            if (c.jerr && !worst) worst = c.jerr;
-            const int s = o.use_1se ? c.idx_1se : c.idx_min;
-            const double *b = c.beta.data() + (size_t)s * (p + 1);
+            const double *r = sel.data() + rec * (size_t)q;
+            const int jerr = (int)r[0], lmu = (int)r[1];
+            if (jerr > 0 || lmu < 1) return ate_fail(ctx, -3, "outcome fit of fold %d failed (jerr %d)", kb + q, jerr);
+            if (jerr && !worst) worst = jerr;
+            const double *b = r + 4;
             ATE_CUDA(ctx, cudaMemcpyAsync(dbeta.p, b, sizeof(double) * (p + 1), cudaMemcpyHostToDevice, ctx->stream));
             ATE_TRY(ate_i_predict_rows(ctx, dX.p, ld, p, dlists.p + offs[3 * q + 2], 0, (long long)lists[3 * q + 2].size(),
-                                       dbeta.p, c.a0[s], b[p], 2, 1, dm0, dm1));
+                                       dbeta.p, r[3], b[p], 2, 1, dm0, dm1));
             ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-            if (lambda_out) lambda_out[kb - 1 + q] = c.lambda[s];
+            if (lambda_out) lambda_out[kb - 1 + q] = r[2];
         }
     }
     res->ms_outcome = tm.lap_ms();

@@ -277,6 +277,17 @@ gram_fold_rect_kernel(const double *__restrict__ partials, int nchunks, int nblk
     }
 }
 
+// the opt-in to more than 48 KB of dynamic shared memory is per device: remember it per device, not
+// per process (one process may hold contexts on several GPUs)
+int gram_allow_big_smem(ate_ctx *ctx) {
+    static bool done[64] = {false};
+    const int d = ctx->device;
+    if (d >= 0 && d < 64 && done[d]) return 0;
+    ATE_CUDA(ctx, cudaFuncSetAttribute(gram_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_LIMIT));
+    if (d >= 0 && d < 64) done[d] = true;
+    return 0;
+}
+
 }  // namespace
 
 int ate_i_gram_fold(ate_ctx *ctx, const double *partials, int nchunks, int nblk, int p, int ldg, double *G) {
@@ -317,11 +328,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
         // these widths (>= 2 * 96^2 flop per 1.5 KB staged) stays far below the DMMA time.
         if (colidx) return ate_fail(ctx, -1, "gram: a %d-column list does not fit the full-row kernel", ncload);
         if (pp > ld) return ate_fail(ctx, -1, "gram: ld (%lld) < padded column count (%d)", ld, pp);
-        static bool attr_set_w = false;
-        if (!attr_set_w) {
-            ATE_CUDA(ctx, cudaFuncSetAttribute(gram_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_LIMIT));
-            attr_set_w = true;
-        }
+        ATE_TRY(gram_allow_big_smem(ctx));
         auto launch = [&](const double *Xb, int nc, int nblk_l, int wA, long long offB, double **scr_out, int *nchunks_out,
                           double flops) -> int {
             const size_t sb = sizeof(double) * (size_t)G_ROWS * (nc + G_PAD);
@@ -397,11 +404,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
     if (nchunks < 1) nchunks = 1;
     void *scr = nullptr;
     ATE_TRY(ate_gram_scratch(ctx, sizeof(double) * 1024 * (size_t)nblk * nchunks, &scr));
-    static bool attr_set = false;
-    if (!attr_set) {
-        ATE_CUDA(ctx, cudaFuncSetAttribute(gram_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_LIMIT));
-        attr_set = true;
-    }
+    ATE_TRY(gram_allow_big_smem(ctx));
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ctx->profile) {
         ATE_CUDA(ctx, cudaEventCreate(&e0));

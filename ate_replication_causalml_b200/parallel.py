@@ -8,7 +8,8 @@ One process per GPU (torchrun); every rank holds the full inputs (n = 1M x p0 = 
     all-reduce hook, after which every rank holds the same models and selects the same lambda;
   * the bootstrap replicates -- rank r draws replicates [r*B/N, (r+1)*B/N) with the Philox
     stream keyed by replicate id, so the union is identical to the 1-GPU run.
-The gaussian outcome model (a few Gram passes) is replicated.
+The K gaussian outcome fits are dealt over ranks the same way (their selected models meet through
+the hook); design construction, held-out prediction and the score are replicated.
 """
 from __future__ import annotations
 
