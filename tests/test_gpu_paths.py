@@ -317,3 +317,21 @@ def test_r_entry_point_mirrors(engine, oracle):
     o = oracle.crossfit_aipw(xs, d["w"], d["y"], fo, ips, iout)
     assert abs(row["ATE"][0] - o["tau"]) <= 1e-9 * abs(o["tau"])
     assert abs(row["lower_ci"][0] - (o["tau"] - 1.96 * o["se"])) < 1e-9
+
+
+@pytest.mark.parametrize("family", ["gaussian", "binomial"])
+def test_row_permutation_leaves_cv_glmnet_unchanged(engine, family):
+    """Property: shuffling the observations (and their fold ids with them) changes
+    only the order of the sums -- same lambda sequence, same selections, coefficients to rounding."""
+    rng = np.random.default_rng(12)
+    n, p = 6000, 14
+    x = rng.standard_normal((n, p)); x[:, 5] = (x[:, 5] > 0.2)
+    eta = x @ rng.uniform(-0.8, 0.8, p)
+    y = eta + rng.standard_normal(n) if family == "gaussian" else (rng.random(n) < 1 / (1 + np.exp(-eta))).astype(float)
+    fid = (np.arange(n) % 10 + 1).astype(np.int32)
+    perm = rng.permutation(n)
+    a = engine.cv_glmnet(x, y, family, foldid=fid)
+    b = engine.cv_glmnet(x[perm], y[perm], family, foldid=fid[perm])
+    assert a["lmu"] == b["lmu"] and (a["idx_min"], a["idx_1se"]) == (b["idx_min"], b["idx_1se"])
+    assert np.abs(a["lambda_"] - b["lambda_"]).max() <= 1e-12 * a["lambda_"][0]
+    assert np.abs(a["beta"] - b["beta"]).max() <= 1e-8 and np.abs(a["cvm"] - b["cvm"]).max() <= 1e-9 * a["cvm"].max()

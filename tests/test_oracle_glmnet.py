@@ -217,3 +217,53 @@ def test_lm_qr_matches_normal_equations_and_summary_formulas(oracle):
     r2, r0 = oracle.lm(x2, y), oracle.lm(x, y)
     assert np.isnan(r2["coef"][[4, 8]]).all() and r2["rank"] == p + 1
     assert np.abs(r2["coef"][[0, 1, 2, 3, 5, 6, 7]] - r0["coef"]).max() < 1e-12
+
+
+# ---------------------------------------------------------------- properties
+@pytest.mark.parametrize("family", ["gaussian", "binomial"])
+def test_row_permutation_leaves_the_path_unchanged(oracle, family):
+    rng = np.random.default_rng(3)
+    n, p = 800, 9
+    x = rng.standard_normal((n, p)); x[:, 2] = (x[:, 2] > 0.3)
+    eta = x @ rng.uniform(-1, 1, p)
+    y = eta + rng.standard_normal(n) if family == "gaussian" else (rng.random(n) < 1 / (1 + np.exp(-eta))).astype(float)
+    perm = rng.permutation(n)
+    a, b = oracle.glmnet(x, y, family), oracle.glmnet(x[perm], y[perm], family)
+    assert a["lmu"] == b["lmu"]
+    assert np.abs(a["lambda_"] - b["lambda_"]).max() <= 1e-12 * a["lambda_"][0]
+    assert np.abs(a["beta"] - b["beta"]).max() <= 1e-9          # sums in another order: rounding only
+    fid = (np.arange(n) % 10 + 1).astype(np.int32)
+    ca, cb = oracle.cv_glmnet(x, y, fid, family), oracle.cv_glmnet(x[perm], y[perm], fid[perm], family)
+    assert (ca["idx_min"], ca["idx_1se"]) == (cb["idx_min"], cb["idx_1se"])
+    assert np.abs(ca["cvm"] - cb["cvm"]).max() <= 1e-9 * ca["cvm"].max()
+    relabel = (10 - fid + 1).astype(np.int32)                     # fold labels are names, not an order
+    cc = oracle.cv_glmnet(x, y, relabel, family)
+    assert np.abs(ca["cvm"] - cc["cvm"]).max() <= 1e-12 * ca["cvm"].max()
+    assert np.abs(ca["cvsd"] - cc["cvsd"]).max() <= 1e-10 * ca["cvsd"].max()
+
+
+def test_aipw_and_bootstrap_identities_hypothesis(oracle):
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.integers(5, 200), st.integers(0, 2**31 - 1))
+    def prop(n, seed):
+        rng = np.random.default_rng(seed)
+        w = (rng.random(n) < 0.5).astype(float); y = (rng.random(n) < 0.4).astype(float)
+        p = rng.uniform(0.05, 0.95, n); m0 = rng.uniform(0, 1, n); m1 = rng.uniform(0, 1, n)
+        tau, se, e1, e2 = oracle.aipw(w, y, p, m0, m1, want_scores=True)
+        # the definition, ate_functions.R:241-243 and :255-256
+        est1 = w * (y - m1) / p + (1 - w) * (y - m0) / (1 - p)
+        assert abs(tau - (est1.mean() + (m1 - m0).mean())) <= 1e-12 * max(1.0, abs(tau))
+        ii = w * y / p - m1 * (w - p) / p - ((1 - w) * y / (1 - p) + m0 * (w - p) / (1 - p)) - tau
+        assert abs(se - np.sqrt((ii ** 2).sum()) / n) <= 1e-12 * se
+        # a replicate over the identity index is the point estimate; over a permutation too
+        ident = np.arange(1, n + 1, dtype=np.int32)
+        assert abs(oracle.tau_hat_dr_est(w, y, p, m0, m1, ident) - tau) <= 1e-12 * max(1.0, abs(tau))
+        perm = rng.permutation(n)
+        assert abs(oracle.tau_hat_dr_est(w, y, p, m0, m1, (perm + 1).astype(np.int32)) - tau) <= 1e-12 * max(1.0, abs(tau))
+        # a replicate is a function of the scores alone (nuisances are not refit, :267-283)
+        idx = rng.integers(1, n + 1, n).astype(np.int32)
+        assert abs(oracle.tau_hat_dr_est(w, y, p, m0, m1, idx) - (e1[idx - 1].mean() + e2[idx - 1].mean())) <= 1e-12
+
+    prop()
