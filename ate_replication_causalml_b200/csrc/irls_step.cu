@@ -618,7 +618,16 @@ struct StepPlan {
                     for (size_t k = 0; k < d.size(); ++k)
                         tab[(size_t)ntr * F_PLAN_W + 8 * (k / per) + (k % per)] = d[k];
                     ngroups[ntr] = g;
-                    max_tiles[ntr] = T;
+                    max_tiles[ntr] = 0;  // the busiest warp's real load (a row wider than T sits alone in a bin)
+                    for (const uint2 &e : d) {
+                        const int sgm = (int)(e.x & 0xffu), cnt = (int)((e.x >> 8) & 0xffu);
+                        int load = 0;
+                        for (int u = 0; u < cnt; ++u) {
+                            const int r = (int)((e.y >> (8 * u)) & 0xffu);
+                            load += r - 4 * sgm + 1 < 4 ? r - 4 * sgm + 1 : 4;
+                        }
+                        if (load > max_tiles[ntr]) max_tiles[ntr] = load;
+                    }
                     return;
                 }
             }
@@ -670,6 +679,22 @@ const StepPlan &step_plan() {
 }
 
 }  // namespace
+
+extern "C" int ate_step_plan_describe(int list_cols, int *ngroups, int *max_tiles, unsigned *desc) {
+    if (list_cols < 0) return -1;
+    const int ntr = (list_cols + 7) / 8;
+    if (ntr > F_MAX_NTR) return -1;
+    const StepPlan &plan = step_plan();
+    if (plan.ngroups[ntr] < 1) return -1;
+    if (ngroups) *ngroups = plan.ngroups[ntr];
+    if (max_tiles) *max_tiles = plan.max_tiles[ntr];
+    if (desc)
+        for (int k = 0; k < F_PLAN_W; ++k) {
+            desc[2 * k] = plan.tab[(size_t)ntr * F_PLAN_W + k].x;
+            desc[2 * k + 1] = plan.tab[(size_t)ntr * F_PLAN_W + k].y;
+        }
+    return 0;
+}
 
 int ate_i_irls_step(ate_ctx *ctx, const IrlsStep &in) {
     if (in.nrows <= 0 || in.ni <= 0) return ate_fail(ctx, -1, "irls_step: bad shape");

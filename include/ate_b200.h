@@ -247,6 +247,15 @@ ATE_API int ate_weighted_gram(ate_ctx *ctx, long long n, int p, const double *x,
                       const double *v, const int32_t *rows, long long nrows, double *G,
                       int on_device);
 
+/* ---- introspection of the fused IRLS step's work plan (host only; no device call) --------- */
+/* No counterpart in the reference.  For a column list of `list_cols` columns (the strong set plus
+ * candidates the binomial fit restricts its Gram to) returns how the 8x8 tiles of the Gram's lower
+ * triangle are dealt to MMA warps: *ngroups CTAs per row chunk, *max_tiles on the busiest warp, and in
+ * desc[2 * 128] one (x, y) pair per warp slot (8 slots per CTA): x = segment | count << 8, y = up to
+ * four tile-row numbers, one per byte.  Lets tests check on a CPU-only box that every tile
+ * is computed exactly once for every width.  Returns -1 for widths the step cannot take. */
+ATE_API int ate_step_plan_describe(int list_cols, int *ngroups, int *max_tiles, unsigned *desc);
+
 #ifdef __cplusplus
 }
 #endif

@@ -131,3 +131,42 @@ def test_two_rank_gloo_exchange(tmp_path):
     outs = [p.communicate(timeout=180)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
+
+
+def test_fused_step_work_plan_covers_every_tile_once_for_every_width():
+    """The fused IRLS step deals the 8x8 tiles of the list Gram's lower triangle to MMA warps from a
+    host-built plan (csrc/irls_step.cu).  For every list width it can take: each tile (r, c <= r) is
+    owned by exactly one warp, a warp holds <= 4 tile rows of ONE 32-column segment and <= 16 tiles,
+    the descriptors fit the launched grid, and narrow lists stay on warps 0-3 (one per SM
+    sub-partition)."""
+    from ate_replication_causalml_b200 import _lib
+    lib = _lib.load()
+    desc = (C.c_uint * 256)()
+    ng, mt = C.c_int(), C.c_int()
+    assert lib.ate_step_plan_describe(417, C.byref(ng), C.byref(mt), desc) == -1      # wider than the staging ring
+    for cols in range(0, 417):
+        assert lib.ate_step_plan_describe(cols, C.byref(ng), C.byref(mt), desc) == 0, cols
+        ntr = (cols + 7) // 8
+        owned = {}
+        busiest = 0
+        for k in range(128):
+            x, y = desc[2 * k], desc[2 * k + 1]
+            seg, cnt = x & 0xFF, (x >> 8) & 0xFF
+            if cnt == 0:
+                continue
+            assert k < 8 * ng.value and 1 <= cnt <= 4
+            tiles = 0
+            for u in range(cnt):
+                r = (y >> (8 * u)) & 0xFF
+                assert 4 * seg <= r < ntr
+                for n in range(min(4, r - 4 * seg + 1)):
+                    key = (r, 4 * seg + n)
+                    assert key not in owned, (cols, key)
+                    owned[key] = k
+                    tiles += 1
+            assert tiles <= 16
+            busiest = max(busiest, tiles)
+        assert set(owned) == {(r, c) for r in range(ntr) for c in range(r + 1)}, cols
+        assert busiest == (mt.value if ntr else 0)
+        if 0 < cols <= 64:
+            assert ng.value == 1 and all(k % 8 < 4 for k in owned.values())
