@@ -86,6 +86,8 @@ SIGNATURES = {
     "ate_crossfit_aipw": (C.c_int, [_vp, C.POINTER(CrossfitOpts), c_ll, C.c_int, _vp, _vp, _vp, _vp,
                                     _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                     C.POINTER(CrossfitResult)]),
+    "ate_cv_select": (C.c_int, [C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int),
+                                C.POINTER(C.c_int)]),
     "ate_step_plan_describe": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), _vp]),
     "ate_weighted_gram": (C.c_int, [_vp, c_ll, C.c_int, _vp, c_ll, _vp, _vp, c_ll, _vp, C.c_int]),
 }

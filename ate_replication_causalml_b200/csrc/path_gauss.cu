@@ -379,6 +379,21 @@ void ate_host_cv_summary(const std::vector<double> &cvk, const std::vector<doubl
     *idx_1se = i1;
 }
 
+extern "C" int ate_cv_select(int nfolds, int lmu, const double *cvraw, const double *fold_weights, const int *fold_nlam,
+                             const double *lambda, double *cvm, double *cvsd, int *idx_min, int *idx_1se) {
+    if (nfolds < 2 || lmu < 1 || !cvraw || !fold_weights || !lambda || !cvm || !cvsd || !idx_min || !idx_1se) return -1;
+    std::vector<double> cvk(cvraw, cvraw + (size_t)nfolds * lmu), wk(fold_weights, fold_weights + nfolds), m, sd;
+    std::vector<int> nlk(nfolds, lmu);
+    if (fold_nlam)
+        for (int f = 0; f < nfolds; ++f) nlk[f] = fold_nlam[f] < lmu ? fold_nlam[f] : lmu;
+    ate_host_cv_summary(cvk, wk, nlk, nfolds, lmu, lambda, m, sd, idx_min, idx_1se);
+    for (int l = 0; l < lmu; ++l) {
+        cvm[l] = m[l];
+        cvsd[l] = sd[l];
+    }
+    return 0;
+}
+
 int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int iy, int i1,
                       const double *vp_host, const PathOpts &po, const std::vector<CvProblem> &probs,
                       std::vector<CvOut> &outs) {

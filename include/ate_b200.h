@@ -247,6 +247,19 @@ ATE_API int ate_weighted_gram(ate_ctx *ctx, long long n, int p, const double *x,
                       const double *v, const int32_t *rows, long long nrows, double *G,
                       int on_device);
 
+/* ---- cv.glmnet's summary of per-fold errors (cvstats + getmin; behind ate_functions.R:101-103,
+ * :123-125, :139-141, :304-305 and the `lambda.min` / `lambda.1se` reads at :106,128,144,308) ------- */
+/* Host only.  cvraw[nfolds x lmu] (row per fold): the fold's mean held-out error at each lambda;
+ * fold_weights[nfolds]: held-out observation counts; fold_nlam[nfolds] (or NULL = lmu everywhere):
+ * how many lambdas each fold's path reached (folds that stopped early drop out of the later
+ * columns).  Writes cvm[lmu] (weighted mean), cvsd[lmu] (sqrt(weighted var / (folds - 1))) and the
+ * 0-based indices of lambda.min (largest lambda attaining the minimum) and lambda.1se (largest
+ * lambda with cvm <= cvm[min] + cvsd[min]).  ate_cv_glmnet does this internally; the entry point is
+ * for callers that hold their own fold errors. */
+ATE_API int ate_cv_select(int nfolds, int lmu, const double *cvraw, const double *fold_weights,
+                          const int *fold_nlam, const double *lambda, double *cvm, double *cvsd,
+                          int *idx_min, int *idx_1se);
+
 /* ---- introspection of the fused IRLS step's work plan (host only; no device call) --------- */
 /* No counterpart in the reference.  For a column list of `list_cols` columns (the strong set plus
  * candidates the binomial fit restricts its Gram to) returns how the 8x8 tiles of the Gram's lower

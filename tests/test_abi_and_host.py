@@ -170,3 +170,34 @@ def test_fused_step_work_plan_covers_every_tile_once_for_every_width():
         assert busiest == (mt.value if ntr else 0)
         if 0 < cols <= 64:
             assert ng.value == 1 and all(k % 8 < 4 for k in owned.values())
+
+
+def test_cv_select_is_cv_glmnets_summary():
+    """ate_cv_select = cvstats + getmin of cv.glmnet (grouped = TRUE): weighted fold mean, sd =
+    sqrt(weighted var / (folds - 1)), lambda.min = LARGEST lambda at the minimum, lambda.1se = largest
+    lambda within one sd of it; folds whose path stopped early leave the later columns."""
+    from ate_replication_causalml_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(8)
+    F, L = 10, 37
+    lam = np.exp(np.linspace(0, -6, L))
+    base = (np.linspace(-1, 1, L) ** 2)[None, :] + 1.0
+    cvraw = np.ascontiguousarray(base + 0.05 * rng.standard_normal((F, L)))
+    wts = rng.integers(80, 120, F).astype(np.float64)
+    nl = np.full(F, L, np.int32); nl[3] = 30; nl[7] = 35
+    cvm = np.empty(L); cvsd = np.empty(L); imin = C.c_int(); i1 = C.c_int()
+    ptr = _lib.ptr
+    assert lib.ate_cv_select(F, L, ptr(cvraw), ptr(wts), ptr(nl), ptr(lam), ptr(cvm), ptr(cvsd), C.byref(imin), C.byref(i1)) == 0
+    for l in range(L):
+        use = nl > l
+        m = np.average(cvraw[use, l], weights=wts[use])
+        v = np.average((cvraw[use, l] - m) ** 2, weights=wts[use]) / (use.sum() - 1)
+        assert abs(cvm[l] - m) < 1e-14 and abs(cvsd[l] - np.sqrt(v)) < 1e-14
+    assert imin.value == int(np.argmin(cvm))
+    assert i1.value == int(np.nonzero(cvm <= cvm[imin.value] + cvsd[imin.value])[0][0])    # lambda is decreasing
+    assert i1.value <= imin.value
+    # ties go to the larger lambda
+    flat = np.ones((F, 4)); lam4 = np.array([4.0, 3.0, 2.0, 1.0]); c4 = np.empty(4); s4 = np.empty(4)
+    assert lib.ate_cv_select(F, 4, ptr(flat), ptr(wts), None, ptr(lam4), ptr(c4), ptr(s4), C.byref(imin), C.byref(i1)) == 0
+    assert (imin.value, i1.value) == (0, 0) and np.allclose(c4, 1.0) and np.allclose(s4, 0.0)
+    assert lib.ate_cv_select(1, 4, ptr(flat), ptr(wts), None, ptr(lam4), ptr(c4), ptr(s4), C.byref(imin), C.byref(i1)) == -1
