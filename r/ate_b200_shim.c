@@ -82,6 +82,23 @@ SEXP C_ate_aipw_score(SEXP ctx, SEXP w, SEXP y, SEXP p, SEXP m0, SEXP m1) {
     return out;
 }
 
+/* glm(y ~ ., family = binomial(link = "logit"))  -- ate_functions.R:218-220, 231-234 (also :25-27, :160-162).
+ * x is model.matrix(...) without the "(Intercept)" column; returns coef with (Intercept) first. */
+SEXP C_ate_glm_binomial(SEXP ctx, SEXP x, SEXP y) {
+    ate_ctx *c = ctx_of(ctx);
+    const int n = Rf_nrows(x), p = Rf_ncols(x);
+    SEXP coef = PROTECT(Rf_allocVector(REALSXP, p + 1));
+    double dev;
+    int iters, conv;
+    int rc = ate_glm_binomial(c, n, p, REAL(x), REAL(y), 25, 1e-8, REAL(coef), &dev, &iters, &conv);
+    FAIL_IF(rc, c, "ate_glm_binomial");
+    if (!conv) Rf_warning("glm.fit: algorithm did not converge");
+    Rf_setAttrib(coef, Rf_install("deviance"), Rf_ScalarReal(dev));
+    Rf_setAttrib(coef, Rf_install("iter"), Rf_ScalarInteger(iters));
+    UNPROTECT(1);
+    return coef;
+}
+
 /* the bootstrap loop  -- ate_functions.R:245-252; idx = NULL -> on-device Philox */
 SEXP C_ate_bootstrap(SEXP ctx, SEXP w, SEXP y, SEXP p, SEXP m0, SEXP m1, SEXP B, SEXP idx, SEXP seed) {
     ate_ctx *c = ctx_of(ctx);

@@ -11,8 +11,12 @@ ate_ctx <- function(device = 0L) {
   # cv.glmnet draws foldid = sample(rep(seq(nfolds), length = N)) from R's RNG; do it here so the
   # global stream advances exactly as with glmnet, then hand the ids down (validation mode)
   if (is.null(foldid)) foldid <- sample(rep(seq(nfolds), length = nrow(x)))
-  .Call("C_ate_cv_glmnet", ate_ctx(), as.integer(family), x, as.double(y), penalty.factor,
-        as.integer(max(foldid)), as.integer(foldid), 0L)
+  m <- .Call("C_ate_cv_glmnet", ate_ctx(), as.integer(family), x, as.double(y), penalty.factor,
+             as.integer(max(foldid)), as.integer(foldid), 0L)
+  k <- seq_len(m$lmu)                    # the buffers hold nlambda = 100 slots; the path may stop earlier
+  m$lambda <- m$lambda[k]; m$a0 <- m$a0[k]; m$beta <- m$beta[, k, drop = FALSE]
+  m$cvm <- m$cvm[k]; m$cvsd <- m$cvsd[k]; m$dev.ratio <- m$dev.ratio[k]
+  m
 }
 
 # ate_functions.R:89-108
@@ -108,7 +112,7 @@ prop_score_ols <- function(dataset, p, treatment_var, outcome_var, method = "Pro
 
 # ate_functions.R:286-328 -- expansion, both cv.glmnet fits and the post-lasso OLS on the library
 belloni <- function(dataset, treatment_var, outcome_var, method = "Belloni et.al") {
-  x <- .Call("C_ate_expand_deg2", ate_ctx(), as.matrix(dataset[, covariates]), TRUE)      # :288-296 (+ mains)
+  x <- .Call("C_ate_expand_deg2", ate_ctx(), as.matrix(dataset[, covariates]))            # :288-296 (mains, then products)
   w <- as.matrix(dataset[treatment_var]); y <- as.matrix(dataset[outcome_var])
   model_xw <- .cv_glmnet_b200(x, w, 0L); model_xy <- .cv_glmnet_b200(x, y, 0L)            # :304-305
   s <- model_xw$lambda[model_xw$idx.min]
