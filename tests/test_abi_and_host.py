@@ -102,32 +102,52 @@ import os, sys
 sys.path.insert(0, sys.argv[1])
 import numpy as np
 import torch.distributed as dist
-from ate_replication_causalml_b200.parallel import TorchComm, replicate_shard, r_sd
-dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % sys.argv[2], rank=int(sys.argv[3]), world_size=2)
+import ctypes as C
+from ate_replication_causalml_b200.parallel import TorchComm, replicate_shard, r_sd, install_allreduce
+W = int(sys.argv[4])
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % sys.argv[2], rank=int(sys.argv[3]), world_size=W)
 comm = TorchComm(dist, None)
 # 1. the hook's contract: each rank fills the entries it owns, zeros elsewhere, sum = union
 buf = np.zeros(10)
-buf[comm.rank::2] = np.arange(10)[comm.rank::2] + 0.5
+buf[comm.rank::W] = np.arange(10)[comm.rank::W] + 0.5
 comm.allreduce_sum_host(buf)
 assert np.array_equal(buf, np.arange(10) + 0.5), buf
 # 2. replicate shards gathered in replicate order
 B = 7
 full = np.arange(B) * 1.25
-lo, hi = replicate_shard(B, comm.rank, 2)
-got = comm.allgather_host(full[lo:hi].copy(), [replicate_shard(B, r, 2)[1] - replicate_shard(B, r, 2)[0] for r in range(2)])
+lo, hi = replicate_shard(B, comm.rank, W)
+got = comm.allgather_host(full[lo:hi].copy(), [replicate_shard(B, r, W)[1] - replicate_shard(B, r, W)[0] for r in range(W)])
 assert np.array_equal(got, full), got
 assert abs(r_sd(got) - full.std(ddof=1)) < 1e-14
+# 3. the C callback the library calls (ate_allreduce_fn): records of the fits a rank solved, zeros for the
+#    others -- the exchange of the full-data fits and of the outcome models (5 fits dealt round-robin)
+class FakeLib:
+    def ate_ctx_set_allreduce(self, h, cb, user):
+        return 0
+class FakeEngine:
+    _lib = FakeLib(); _h = None
+eng = FakeEngine()
+install_allreduce(eng, comm)
+rec, K = 6, 5
+want = np.arange(rec * K, dtype=np.float64).reshape(K, rec) + 1.0
+mine = np.zeros_like(want)
+for k in range(K):
+    if k % W == comm.rank:
+        mine[k] = want[k]
+rc = eng._allreduce_cb(None, mine.ctypes.data_as(C.POINTER(C.c_double)), mine.size)
+assert rc == 0 and np.array_equal(mine, want), mine
 dist.destroy_process_group()
 print("ok", comm.rank)
 """
 
 
-def test_two_rank_gloo_exchange(tmp_path):
+@pytest.mark.parametrize("world", [2, 4])
+def test_gloo_exchange_between_ranks(tmp_path, world):
     script = tmp_path / "worker.py"
     script.write_text(_WORKER)
-    port = str(29500 + os.getpid() % 2000)
-    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r)], stdout=subprocess.PIPE,
-                              stderr=subprocess.STDOUT, text=True) for r in range(2)]
+    port = str(29500 + (os.getpid() + 7 * world) % 2000)
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, port, str(r), str(world)], stdout=subprocess.PIPE,
+                              stderr=subprocess.STDOUT, text=True) for r in range(world)]
     outs = [p.communicate(timeout=180)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
