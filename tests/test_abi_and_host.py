@@ -221,3 +221,27 @@ def test_cv_select_is_cv_glmnets_summary():
     assert lib.ate_cv_select(F, 4, ptr(flat), ptr(wts), None, ptr(lam4), ptr(c4), ptr(s4), C.byref(imin), C.byref(i1)) == 0
     assert (imin.value, i1.value) == (0, 0) and np.allclose(c4, 1.0) and np.allclose(s4, 0.0)
     assert lib.ate_cv_select(1, 4, ptr(flat), ptr(wts), None, ptr(lam4), ptr(c4), ptr(s4), C.byref(imin), C.byref(i1)) == -1
+
+
+def test_docs_name_kernels_and_entry_points_that_exist():
+    """DESIGN.md / INTEGRATION.md must not drift from the code: every `*_kernel` they name is defined in
+    csrc/, every `ate_*` entry point they name is declared in the header, and every declared entry
+    point is either tied to reference lines or marked as having no counterpart."""
+    csrc = os.path.join(ROOT, "ate_replication_causalml_b200", "csrc")
+    code = "".join(open(os.path.join(csrc, f)).read() for f in os.listdir(csrc) if f.endswith((".cu", ".cuh")))
+    kernels = set(re.findall(r"\b(\w+_kernel)\b\s*(?:<[^>]*>)?\s*\(", code))
+    docs = open(os.path.join(ROOT, "DESIGN.md")).read() + open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    for k in set(re.findall(r"`(\w+_kernel)`", docs)):
+        assert k in kernels, f"{k} is named in the docs but not defined in csrc/"
+    declared = set(_declared_symbols())
+    skip = {"ate_b200", "ate_ctx", "ate_crossfit_opts", "ate_crossfit_result", "ate_allreduce_fn", "ate_functions",
+            "ate_replication", "ate_oracle", "ate_host_cv_summary", "ate_elnet_path", "ate_lognet_path"}
+    for name in set(re.findall(r"`(ate_[a-z0-9_]+)`", docs)):
+        if name in skip or name.startswith(("ate_i_", "ate_replication_", "ate_functions")):
+            continue
+        if name in ("ate_condmean_lasso", "ate_lasso", "ate_condmean_ols"):      # R closures, not C entry points
+            continue
+        assert name in declared, f"{name} is named in the docs but not declared in include/ate_b200.h"
+    hdr = open(os.path.join(ROOT, "include", "ate_b200.h")).read()
+    assert re.search(r"ate_functions\.R:\d+", hdr) and re.search(r"ate_replication\.Rmd:\d+", hdr)
+    assert hdr.count("counterpart") >= 3          # ctx / hooks / static score / introspection say so explicitly
