@@ -267,3 +267,19 @@ def test_aipw_and_bootstrap_identities_hypothesis(oracle):
         assert abs(oracle.tau_hat_dr_est(w, y, p, m0, m1, idx) - (e1[idx - 1].mean() + e2[idx - 1].mean())) <= 1e-12
 
     prop()
+
+
+@pytest.mark.parametrize("tag,n,p0", [("a", 200, 5), ("b", 5000, 21)])
+def test_glm_and_lm_regression_fixtures(oracle, golden, tag, n, p0):
+    """Pins of the oracle's glm.fit / lm restatements on the fixture inputs (tools/make_golden.py)."""
+    reg = golden["reg"]
+    d = synth.make_dataset(n, p0)
+    xs, _, _ = oracle.scale(d["x_raw"], cols=np.arange(d["n_continuous"]))
+    xw = np.column_stack([xs, d["w"]])
+    gm, gp = oracle.glm_binomial(xw, d["y"]), oracle.glm_binomial(xs, d["w"])
+    assert [gm["iters"], gp["iters"]] == reg[f"{tag}_glm_iters"].tolist()
+    assert np.abs(gm["coef"] - reg[f"{tag}_glm_out"]).max() < 1e-11 and np.abs(gp["coef"] - reg[f"{tag}_glm_ps"]).max() < 1e-11
+    assert np.allclose([gm["deviance"], gp["deviance"]], reg[f"{tag}_glm_dev"], rtol=1e-12)
+    lm = oracle.lm(xw, d["y"])
+    assert np.abs(lm["coef"] - reg[f"{tag}_lm_coef"]).max() < 1e-12 and np.abs(lm["std_err"] - reg[f"{tag}_lm_se"]).max() < 1e-12
+    assert abs(lm["sigma"] - float(reg[f"{tag}_lm_sigma"])) < 1e-13
