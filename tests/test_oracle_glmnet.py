@@ -283,3 +283,16 @@ def test_glm_and_lm_regression_fixtures(oracle, golden, tag, n, p0):
     lm = oracle.lm(xw, d["y"])
     assert np.abs(lm["coef"] - reg[f"{tag}_lm_coef"]).max() < 1e-12 and np.abs(lm["std_err"] - reg[f"{tag}_lm_se"]).max() < 1e-12
     assert abs(lm["sigma"] - float(reg[f"{tag}_lm_sigma"])) < 1e-13
+
+
+def test_glm_binomial_against_sklearn_unpenalised_logistic(oracle):
+    """Independent check of the glm.fit restatement: scikit-learn's unpenalised logistic regression
+    (a different algorithm, L-BFGS) lands on the same MLE."""
+    from sklearn.linear_model import LogisticRegression
+    rng = np.random.default_rng(21)
+    n, p = 3000, 5
+    x = rng.standard_normal((n, p))
+    y = (rng.random(n) < 1 / (1 + np.exp(-(x @ np.array([0.5, -1.0, 0.0, 0.3, 0.8]) - 0.2)))).astype(float)
+    g = oracle.glm_binomial(x, y)
+    sk = LogisticRegression(penalty=None, tol=1e-12, max_iter=5000).fit(x, y)
+    assert np.abs(np.r_[sk.intercept_, sk.coef_[0]] - g["coef"]).max() < 1e-5
