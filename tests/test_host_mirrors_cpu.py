@@ -49,6 +49,14 @@ class OracleEngine:
     def r_sample(self, n, k, kind):
         return self.O.sample_replace(n, k, kind)
 
+    def crossfit_aipw(self, x, w, y, foldid=None, inner_ps=None, inner_out=None, boot_idx=None, B=0, **kw):
+        self.calls.append(("crossfit_aipw", dict(kw, B=B)))
+        o = self.O.crossfit_aipw(x, w, y, foldid, inner_ps, inner_out, use_1se=bool(kw.get("use_1se", 1)))
+        r = dict(tau=o["tau"], se_sandwich=o["se"], se_bootstrap=float("nan"), phat=o["phat"], m0=o["m0"], m1=o["m1"])
+        if B > 0:
+            r["se_bootstrap"], r["boot"] = self.O.bootstrap_idx(w, y, o["phat"], o["m0"], o["m1"], boot_idx)
+        return r
+
 
 @pytest.fixture()
 def setup(oracle):
@@ -137,3 +145,20 @@ def test_belloni_quirks(setup, oracle):
     row = af.belloni(df, "W", "Y", foldid_xw=f1, foldid_xy=f2)
     o = oracle.lm(np.column_stack([x[:, c_union - 1], df["W"].to_numpy()]), df["Y"].to_numpy())
     assert abs(row["ATE"][0] - o["coef"][-1]) < 1e-12 and row["Method"][0] == "Belloni et.al"
+
+
+def test_crossfit_mirror_frame_and_options(setup, oracle):
+    from conftest import make_folds
+    df, names, d, eng = setup
+    n = len(df)
+    fo, ips, iout = make_folds(n)
+    oracle.set_seed(2)
+    bidx = np.stack([oracle.sample_replace(n, n, 1) for _ in range(9)])
+    row = af.crossfit_aipw(df, "W", "Y", B=9, foldid=fo, inner_ps=ips, inner_out=iout, boot_idx=bidx)
+    det = row.attrs["detail"]
+    name, opts = eng.calls[-1]
+    assert name == "crossfit_aipw" and opts["B"] == 9 and opts["boot_mode"] == 0 and opts["K"] == 5 and opts["use_1se"] == 1
+    assert list(row.columns) == ["Method", "ATE", "lower_ci", "upper_ci"]
+    assert row["ATE"][0] == det["tau"] and abs(row["upper_ci"][0] - (det["tau"] + 1.96 * det["se_bootstrap"])) < 1e-15
+    row2 = af.crossfit_aipw(df, "W", "Y", bootstrap_se=False, foldid=fo, inner_ps=ips, inner_out=iout)
+    assert eng.calls[-1][1]["B"] == 0 and abs(row2["lower_ci"][0] - (det["tau"] - 1.96 * det["se_sandwich"])) < 1e-15
