@@ -128,7 +128,9 @@ extern "C" int ate_cv_glmnet(ate_ctx *ctx, int family, long long n, int p, const
         ATE_TRY(check_foldid(ctx, foldid, n, nfolds, "ate_cv_glmnet"));
         fid.assign(foldid, foldid + n);
     } else {
-        ate_host_rng_seed(&ctx->rng, seed);
+        // seed != 0: set.seed(seed) first; seed == 0: continue the ctx's stream, as consecutive
+        // cv.glmnet() calls do in one R session (a stream that was never seeded starts at set.seed(0))
+        if (seed != 0 || !ctx->rng.seeded) ate_host_rng_seed(&ctx->rng, seed);
         ate_host_foldid(&ctx->rng, (int)n, nfolds, rng_kind, fid.data());
     }
     DevBuf<double> dX;

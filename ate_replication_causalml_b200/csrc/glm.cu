@@ -149,7 +149,10 @@ extern "C" int ate_glm_binomial(ate_ctx *ctx, long long n, int p, const double *
         if (it <= 1) launch_update<1>(ctx, dX.p, ld, n, p, dcoef.p, init, dw.p, dpart.p, blocks);
         else if (it <= 2) launch_update<2>(ctx, dX.p, ld, n, p, dcoef.p, init, dw.p, dpart.p, blocks);
         else if (it <= 4) launch_update<4>(ctx, dX.p, ld, n, p, dcoef.p, init, dw.p, dpart.p, blocks);
-        else launch_update<8>(ctx, dX.p, ld, n, p, dcoef.p, init, dw.p, dpart.p, blocks);
+        else if (it <= 8) launch_update<8>(ctx, dX.p, ld, n, p, dcoef.p, init, dw.p, dpart.p, blocks);
+        else if (it <= 16) launch_update<16>(ctx, dX.p, ld, n, p, dcoef.p, init, dw.p, dpart.p, blocks);
+        else if (it <= 32) launch_update<32>(ctx, dX.p, ld, n, p, dcoef.p, init, dw.p, dpart.p, blocks);
+        else return ate_fail(ctx, -1, "ate_glm_binomial: a %lld-column row is wider than the update kernel takes", ld);
         ATE_LAUNCHED(ctx);
         ATE_CUDA(ctx, cudaMemcpyAsync(hpart.data(), dpart.p, sizeof(double) * blocks, cudaMemcpyDeviceToHost, ctx->stream));
         ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

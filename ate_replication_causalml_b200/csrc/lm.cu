@@ -199,7 +199,10 @@ extern "C" int ate_lm(ate_ctx *ctx, long long n, int p, const double *x, const d
     if (it <= 1) launch_resid<1>(ctx, dX.p, ld, n, p, dcoef.p, v, dres.p, dpart.p, blocks);
     else if (it <= 2) launch_resid<2>(ctx, dX.p, ld, n, p, dcoef.p, v, dres.p, dpart.p, blocks);
     else if (it <= 4) launch_resid<4>(ctx, dX.p, ld, n, p, dcoef.p, v, dres.p, dpart.p, blocks);
-    else launch_resid<8>(ctx, dX.p, ld, n, p, dcoef.p, v, dres.p, dpart.p, blocks);
+    else if (it <= 8) launch_resid<8>(ctx, dX.p, ld, n, p, dcoef.p, v, dres.p, dpart.p, blocks);
+    else if (it <= 16) launch_resid<16>(ctx, dX.p, ld, n, p, dcoef.p, v, dres.p, dpart.p, blocks);
+    else if (it <= 32) launch_resid<32>(ctx, dX.p, ld, n, p, dcoef.p, v, dres.p, dpart.p, blocks);
+    else return ate_fail(ctx, -1, "ate_lm: a %lld-column row is wider than the residual kernel takes", ld);
     ATE_LAUNCHED(ctx);
     ATE_CUDA(ctx, cudaMemcpyAsync(hpart.data(), dpart.p, sizeof(double) * 2 * blocks, cudaMemcpyDeviceToHost, ctx->stream));
     if (resid)

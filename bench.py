@@ -1,26 +1,32 @@
 #!/usr/bin/env python
 """bench.py -- cross-fitted AIPW ATE + bootstrap-SE fits/sec (BASELINE.json's metric).
 
-A "step" is one complete fit of SURVEY.md section 8's composite on the C1 workload:
-n = 1,000,000 rows, p0 = 16 base covariates -> the 256 ordered degree-2 products
+Default workload C1 (BASELINE.json configs[1]); a "step" is one complete fit of SURVEY.md section
+8's composite: n = 1,000,000 rows, p0 = 16 base covariates -> the 256 ordered degree-2 products
 (ate_functions.R:290-296), K = 5 cross-fitting folds, cv.glmnet with 10 inner folds and a
-100-lambda path for both nuisances (L1-logistic propensity, lasso outcome), AIPW score,
-sandwich SE and B = 2000 Philox bootstrap replicates.
+100-lambda path for both nuisances (L1-logistic propensity, lasso outcome), AIPW score, sandwich
+SE and B = 2000 Philox bootstrap replicates.
 
-  value : fits/s with the inputs already resident in HBM (device pointers into the C ABI)
-  e2e   : fits/s through the same C-ABI call with HOST (pinned) buffers, H2D/D2H inside
-  roofline : the dominant kernel (fp64 DMMA weighted Gram), algorithmic flop / CUDA-event time
-             of every launch in the timed region, against cuBLAS DGEMM measured in this run
-  cpu_baseline : the CPU oracle (a port: R is not installed) on a bounded sample
+  value        fits/s, inputs already resident in HBM (device pointers into the C ABI), timed with
+               CUDA events on the library's stream, profiling hooks OFF
+  e2e          fits/s through the same C-ABI call with HOST (pinned) buffers: the H2D copies of
+               the inputs and fold ids and the D2H of the nuisances / replicates are inside
+  roofline     the dominant kernel, from a separate short profiled pass (CUDA events around
+               every launch of it on the library's stream)
+  cpu_baseline the CPU oracle (a port: R is not installed) on a bounded sample, all host threads,
+               plus the same sample on ONE thread (what R itself would use)
 
-N > 1 (torchrun): one process per GPU, data replicated, the 50 CV-fold paths of each nuisance
-and the bootstrap replicates are sharded over ranks; held-out CV deviances cross ranks through
-one small all-reduce, replicate estimates through one all-gather.  One fit is timed => "strong".
+Other workloads (--workload C2|C3|C4) are the remaining BASELINE.json configs; their lines carry
+their own metric names and are committed under profiles/.
+
+N > 1 (torchrun): one process per GPU.  The rows are sharded: rank r keeps rows
+[r n / N, (r + 1) n / N) of the design and of every fit's private row copy; each IRLS round's packed
+partial sums (strong-set Grams, X^T r, X^T v, deviance) meet in ONE ncclAllReduce on the library's
+stream; the bootstrap replicates are sharded by replicate id.  One fit is timed => "strong".
 """
 from __future__ import annotations
 
 import argparse
-import ctypes
 import json
 import os
 import subprocess
@@ -36,12 +42,29 @@ import numpy as np  # noqa: E402
 METRIC = "cross-fitted AIPW ATE+bootstrap-SE fits/sec at n=1M,p=256"
 UNIT = "fits/s"
 
+WORKLOADS = {
+    "C1": dict(n=1_000_000, p0=16, expand=1, B=2000,
+               text="C1: cross-fit AIPW, L1-logistic propensity + lasso outcome, degree-2 products, 5 folds, "
+                    "10 inner cv folds, 100-lambda path, Philox bootstrap"),
+    "C2": dict(n=1_000_000, p0=16, expand=1, B=10_000,
+               text="C2: bootstrap ATE standard error, B = 10,000 replicates over the n = 1M AIPW scores"),
+    "C3": dict(n=4_000_000, p0=0, p=1024, B=0,
+               text="C3: 10-fold cv.glmnet lambda selection (gaussian lasso), n = 4M, p = 1024"),
+    "C4": dict(n=16_000_000, p0=22, expand=2, B=2000,
+               text="C4: cross-fit AIPW, n = 16M, p0 = 22 -> 22 mains + 484 ordered products = 506 columns "
+                    "(BASELINE's 'p = 512'), 5 folds, 10 inner cv folds, 100-lambda path, B = 2000"),
+}
+
+
+def design_width(p0, expand):
+    return p0 if expand == 0 else (p0 * p0 if expand == 1 else p0 + p0 * p0)
+
 
 def workload(args):
-    return dict(workload="C1: cross-fit AIPW, L1-logistic propensity + lasso outcome, degree-2 "
-                         "products, 5 folds, 10 inner cv folds, 100-lambda path, Philox bootstrap",
-                n=args.n, p0=args.p0, p=args.p0 * args.p0, K=5, nfolds_inner=10, nlambda=args.nlambda,
-                B=args.B, l2="inputs_exceed_l2 (design matrix %.2f GB)" % (args.n * (args.p0 ** 2 + 32) * 8 / 1e9))
+    p = design_width(args.p0, args.expand)
+    return dict(workload=WORKLOADS[args.workload]["text"], n=args.n, p0=args.p0, p=p, K=5, nfolds_inner=10,
+                nlambda=args.nlambda, B=args.B,
+                l2="inputs_exceed_l2 (design matrix %.2f GB)" % (args.n * (p + 32) * 8 / 1e9))
 
 
 def make_inputs(n, p0):
@@ -132,53 +155,94 @@ def measure_dgemm_peak(torch, dev):
     return 2.0 * N ** 3 / best / 1e9  # TFLOP/s
 
 
+def hbm_peak():
+    try:
+        mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(mp["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy): of measured"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md): of fallback"
+
+
 # ------------------------------------------------------------------------------------------
-def cpu_sample(args, n_sample, threads=None):
-    """The CPU oracle on a bounded sample of the same workload.  Returns (seconds, fits/s
-    scaled linearly in n to the full workload, threads used, description)."""
+def host_threads():
+    """Host threads this process may use (torchrun exports OMP_NUM_THREADS=1: not a property of the box)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_sample(args, n_sample, threads):
+    """One fit of the CPU oracle on a bounded sample of the same workload (same p, K, inner folds and
+    lambdas; n_sample rows; Bs replicates), on exactly `threads` OpenMP threads.  The two legs scale
+    differently and are extrapolated separately: the nuisance fits are linear in n (glmnet's sweeps
+    are O(n) each; checked on one machine in profiles/r02_cpu_linearity.jsonl), the bootstrap is
+    linear in B * n."""
     from oracle import oracle as O
-    if threads:
-        os.environ["OMP_NUM_THREADS"] = str(threads)
-    ncores = threads or os.cpu_count() or 1
+    used = O.set_threads(threads)
     d, fo, ips, iout = make_inputs(n_sample, args.p0)
     xs, _, _ = O.scale(d["x_raw"], cols=np.arange(d["n_continuous"]))
-    xd = O.expand_deg2(xs, False)
-    Bs = max(20, int(args.B * n_sample / args.n))
+    xd = O.expand_deg2(xs, include_main=(args.expand == 2)) if args.expand else xs
+    Bs = max(20, int(round(args.B * n_sample / args.n))) if args.B > 0 else 0
     t = time.perf_counter()
     r = O.crossfit_aipw(xd, d["w"], d["y"], fo, ips, iout, nlambda=args.nlambda)
-    rng = np.random.Generator(np.random.Philox(key=9))
-    bidx = rng.integers(1, n_sample + 1, size=(Bs, n_sample)).astype(np.int32)
-    O.bootstrap_idx(d["w"], d["y"], r["phat"], r["m0"], r["m1"], bidx)
-    dt = time.perf_counter() - t
-    # glmnet's per-sweep cost and the bootstrap are linear in n: scale the sample to n
-    fits_per_s = (1.0 / dt) * (n_sample / args.n)
-    desc = (f"one full fit at n={n_sample} (same p={args.p0 ** 2}, K=5, 10 inner folds, {args.nlambda} lambdas, "
-            f"B={Bs}) took {dt:.1f} s; scaled linearly in n to n={args.n}")
-    return dt, fits_per_s, min(ncores, 10), desc
+    t_fit = time.perf_counter() - t
+    t_boot = 0.0
+    if Bs > 0:
+        rng = np.random.Generator(np.random.Philox(key=9))
+        bidx = rng.integers(1, n_sample + 1, size=(Bs, n_sample)).astype(np.int32)
+        t = time.perf_counter()
+        O.bootstrap_idx(d["w"], d["y"], r["phat"], r["m0"], r["m1"], bidx)
+        t_boot = time.perf_counter() - t
+    full_s = t_fit * (args.n / n_sample) + (t_boot * (args.B * args.n) / (Bs * n_sample) if Bs > 0 else 0.0)
+    return dict(n=n_sample, B=Bs, threads=used, fit_s=t_fit, boot_s=t_boot, sample_s=t_fit + t_boot,
+                full_workload_s=full_s, fits_per_s=1.0 / full_s)
+
+
+def sample_text(args, s):
+    return (f"one full fit of the CPU port at n={s['n']} (same p={design_width(args.p0, args.expand)}, K=5, 10 inner "
+            f"folds, {args.nlambda} lambdas) took {s['fit_s']:.2f} s and B={s['B']} index-mode replicates {s['boot_s']:.2f} s "
+            f"on {s['threads']} threads; extrapolated to n={args.n}, B={args.B}: nuisance fits x{args.n / s['n']:.0f} (linear "
+            f"in n), bootstrap x{(args.B * args.n) / max(1, s['B'] * s['n']):.0f} (linear in B*n) = {s['full_workload_s']:.0f} s "
+            "per fit.  R and glmnet are not installed on this box: the timed code is oracle/ate_oracle.c, a C "
+            "restatement of glmnet's coordinate descent, cv.glmnet and the reference's bootstrap loop")
 
 
 def run_reference(args, rank):
+    """--impl reference: the reference's CPU path (the oracle port) on rank 0, all host threads."""
     if rank != 0:
         return
     t0 = time.perf_counter()
-    vals = []
+    threads = args.cpu_threads or host_threads()
     steps = max(1, args.steps)
-    desc = ""
-    cores = 1
     warm = 1 if args.warmup >= 1 else 0  # one untimed sample pages the oracle library and its threads in
     for _ in range(warm):
-        cpu_sample(args, args.cpu_sample_n)
-    for _ in range(steps):
-        dt, fps, cores, desc = cpu_sample(args, args.cpu_sample_n)
-        vals.append((dt, fps))
-    fps = float(np.mean([v[1] for v in vals]))
-    ms = 1e3 / fps
+        cpu_sample(args, args.cpu_sample_n, threads)
+    runs = [cpu_sample(args, args.cpu_sample_n, threads) for _ in range(steps)]
+    s = dict(runs[0])
+    for k in ("fit_s", "boot_s", "sample_s", "full_workload_s"):
+        s[k] = float(np.mean([r[k] for r in runs]))
+    fps = 1.0 / s["full_workload_s"]
+    one = None
+    if not args.no_single_thread:
+        o = cpu_sample(args, args.cpu_sample_n, 1)
+        one = dict(value=o["fits_per_s"], unit=UNIT, cores=1, kind="port", sample=sample_text(args, o))
+    lin = None
+    if args.linearity:
+        b = cpu_sample(args, 2 * args.cpu_sample_n, threads)
+        lin = dict(n_a=s["n"], fit_s_a=s["fit_s"], n_b=b["n"], fit_s_b=b["fit_s"],
+                   per_row_ratio=(b["fit_s"] / b["n"]) / (s["fit_s"] / s["n"]),
+                   note="seconds per row of the nuisance fits at 2x the sample (1.0 = linear in n)")
+    cfg = workload(args)
+    cfg["sample"] = dict(n=s["n"], B=s["B"], threads=s["threads"],
+                         note="what each timed step actually ran; `value` is that time extrapolated to the n and B "
+                              "above (cpu_baseline.sample states the arithmetic), `ms_per_step` is the sample's own time")
     line = dict(metric=METRIC, value=fps, unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warm,
-                ms_per_step=ms, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f64",
-                data="synthetic", impl="reference", config=workload(args),
-                cpu_baseline=dict(value=fps, unit=UNIT, cores=cores, kind="port",
-                                  sample=desc + " (R and glmnet are not installed on this box: the timed code is "
-                                                "oracle/ate_oracle.c, a C restatement of glmnet's coordinate descent)"),
+                ms_per_step=1e3 * s["sample_s"], ms_per_step_extrapolated=1e3 * s["full_workload_s"],
+                higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f64",
+                data="synthetic", impl="reference", config=cfg,
+                cpu_baseline=dict(value=fps, unit=UNIT, cores=s["threads"], kind="port", sample=sample_text(args, s)),
+                cpu_baseline_1thread=one, linearity=lin,
                 e2e=dict(value=fps, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0, wall_s=time.perf_counter() - t0)
     print(json.dumps(line), flush=True)
@@ -191,14 +255,26 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=1_000_000)
-    ap.add_argument("--p0", type=int, default=16)
-    ap.add_argument("--B", type=int, default=2000)
+    ap.add_argument("--workload", default="C1", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=None)
+    ap.add_argument("--p0", type=int, default=None)
+    ap.add_argument("--B", type=int, default=None)
     ap.add_argument("--nlambda", type=int, default=100)
     ap.add_argument("--cpu-sample-n", type=int, default=10_000)
+    ap.add_argument("--cpu-threads", type=int, default=0, help="threads of the CPU legs (0 = every host thread)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-single-thread", action="store_true")
+    ap.add_argument("--linearity", action="store_true", help="reference arm: time a second sample at 2x the rows")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.n is None:
+        args.n = wl["n"]
+    if args.p0 is None:
+        args.p0 = wl["p0"]
+    if args.B is None:
+        args.B = wl["B"]
+    args.expand = wl.get("expand", 1)
 
     import faulthandler
     faulthandler.dump_traceback_later(int(os.environ.get("ATE_BENCH_WATCHDOG", "1500")), exit=True)  # a stuck run leaves a traceback
@@ -207,13 +283,13 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":
+        if args.workload != "C1":
+            raise SystemExit("bench.py: the reference arm times the headline workload (C1) only")
         run_reference(args, rank)
         return
 
     import torch
     import torch.distributed as dist
-    from ate_replication_causalml_b200.engine import Engine
-    from ate_replication_causalml_b200 import parallel
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the engine has no CPU fallback)")
@@ -227,132 +303,17 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-
-    d, fo, ips, iout = make_inputs(args.n, args.p0)
-    n, p0 = args.n, args.p0
-    # pinned host buffers (e2e leg) and HBM-resident copies (value leg); column-major base matrix
-    xb_host = torch.from_numpy(np.asfortranarray(d["x_raw"]).T.copy()).contiguous().pin_memory()  # (p0, n) == col-major n x p0
-    w_host = torch.from_numpy(d["w"]).pin_memory()
-    y_host = torch.from_numpy(d["y"]).pin_memory()
-    xb_dev, w_dev, y_dev = xb_host.to(dev), w_host.to(dev), y_host.to(dev)
-
-    eng = Engine(local_rank)
-    stream = torch.cuda.ExternalStream(eng.stream_ptr, device=dev)
-    comm = parallel.TorchComm(dist, dev) if world > 1 else None
-
-    def one_fit(on_device: bool):
-        if on_device:
-            return parallel.crossfit_sharded(eng, xb_dev.data_ptr(), w_dev.data_ptr(), y_dev.data_ptr(), n, p0,
-                                             fo, ips, iout, comm=comm, on_device=True, n_continuous=d["n_continuous"],
-                                             expand=1, B=args.B, nlambda=args.nlambda)
-        return parallel.crossfit_sharded(eng, xb_host.numpy().T, w_host.numpy(), y_host.numpy(), n, p0, fo, ips,
-                                         iout, comm=comm, on_device=False, n_continuous=d["n_continuous"],
-                                         expand=1, B=args.B, nlambda=args.nlambda)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(nsteps, on_device):
-        barrier()
-        ev0 = torch.cuda.Event(enable_timing=True)
-        ev1 = torch.cuda.Event(enable_timing=True)
-        ev0.record(stream)
-        last = None
-        for _ in range(nsteps):
-            last = one_fit(on_device)
-        ev1.record(stream)
-        barrier()
-        ms = ev0.elapsed_time(ev1)
-        if world > 1:
-            t = torch.tensor([ms], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, last
-
-    for _ in range(args.warmup):
-        one_fit(True)
-    sampler = ClockSampler(local_rank)
-    launches0 = eng.launches
-    eng.profile_enable(True)
-    sampler.start()
-    ms_total, last = timed(args.steps, True)
-    clocks = sampler.stop()
-    prof = eng.profile_read()
-    eng.profile_enable(False)
-    launches = eng.launches - launches0
-    ms_step = ms_total / args.steps
-    value = 1e3 / ms_step
-
-    e2e = None
-    if not args.no_e2e:
-        one_fit(False)  # warm the host path once
-        ms_e2e, last_h = timed(args.steps, False)
-        h2d = (n * p0 + 2 * n) * 8
-        d2h = 3 * n * 8 + args.B * 8 + 256
-        e2e = dict(value=1e3 / (ms_e2e / args.steps), unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
-                   ms_per_step=ms_e2e / args.steps)
-
-    # ---- roofline of the dominant kernel ----
-    # The dominant kernel is the fused IRLS step (irls_step_kernel): it streams the design rows
-    # once per step (HBM-bound once the Gram is restricted to glmnet's strong set) and runs the
-    # strong-set Gram on the fp64 DMMA pipe from the same staged rows.
-    roof = None
+    import bench_workloads as W
+    ctx = W.BenchCtx(args=args, rank=rank, world=world, local_rank=local_rank, dev=dev, torch=torch, dist=dist)
+    if args.workload in ("C1", "C4"):
+        line = W.run_crossfit(ctx)
+    elif args.workload == "C2":
+        line = W.run_bootstrap(ctx)
+    else:
+        line = W.run_cv_gaussian(ctx)
     if rank == 0:
-        peak_tensor = measure_dgemm_peak(torch, dev)
-        gl = max(1, prof["gram_launches"])
-        avg_ms = prof["gram_ms"] / gl
-        hbm_peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md): of fallback"
-        try:
-            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-            hbm_peak, peak_src = float(mp["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy): of measured"
-        except Exception:
-            pass
-        achieved = prof["gram_bytes"] / gl / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
-        # DRAM bytes of one launch from the committed ncu --set full capture (a smaller launch than
-        # this run's: the ratio to its algorithmic bytes is what carries over)
-        traffic, traffic_capture = None, None
-        try:
-            traffic_capture = json.load(open(os.path.join(ROOT, "profiles", "r01b_irls_step_traffic.json")))
-            traffic = traffic_capture["dram_bytes_per_launch"]
-        except Exception:
-            pass
-        tf = prof["gram_flops"] / gl / (avg_ms * 1e-3) / 1e12 if avg_ms > 0 else 0.0
-        roof = dict(bound="hbm", kernel="irls_step_kernel (fused IRLS step: eta/q/v/r, X^T r, X^T v and the "
-                                        "strong-set Gram X_S^T V X_S on DMMA from one pass over the rows)",
-                    achieved=achieved, peak=hbm_peak, unit="GB/s", frac=achieved / hbm_peak, traffic=traffic,
-                    traffic_capture=traffic_capture,
-                    launches=prof["gram_launches"], avg_launch_ms=avg_ms, share_of_step=prof["gram_ms"] / ms_total,
-                    algorithmic="nrows*(p+2)*8 bytes per launch (each staged row read once, v written once)",
-                    peak_source=peak_src,
-                    tensor=dict(achieved_tflops=tf, peak_tflops=peak_tensor, frac=tf / peak_tensor if peak_tensor else None,
-                                note="fp64 DMMA work of the same launches: nrows*|L|*(|L|+1) flop over the column list L; "
-                                     "peak = cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no fp64 "
-                                     "row). The full-width Gram (gram_dmma_kernel, used by the gaussian fits) reaches "
-                                     "0.81 of that peak: profiles/"))
-
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        dt, fps, cores, desc = cpu_sample(args, args.cpu_sample_n)
-        cpu = dict(value=fps, unit=UNIT, cores=cores, kind="port",
-                   sample=desc + " (R/glmnet are not installed here: oracle/ate_oracle.c restates them)")
-
-    if rank == 0:
-        line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
-                    ms_per_step=ms_step, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="f64",
-                    data="synthetic", config=dict(workload(args), parallelism=("1 GPU" if world == 1 else
-                                                  f"cv-fold paths + bootstrap replicates sharded over {world} GPUs")),
-                    clocks=clocks, e2e=e2e, gpu_launches=int(launches), roofline=roof, cpu_baseline=cpu,
-                    result=dict(tau=last["tau"], se_sandwich=last["se_sandwich"], se_bootstrap=last["se_bootstrap"],
-                                true_ate=d["true_ate"], rounds_irls=last.get("rounds_irls"),
-                                irls_solves=last.get("irls_solves"), strong_mean=last.get("strong_mean"),
-                                strong_frac2=last.get("strong_frac2"),
-                                stage_ms={k: last.get(k) for k in ("ms_design", "ms_outcome", "ms_propensity",
-                                                                    "ms_score", "ms_bootstrap")}))
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
-    eng.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -102,8 +102,10 @@ ATE_API int ate_glmnet(ate_ctx *ctx, int family, long long n, int p, const doubl
 /* ---- cv.glmnet(x, y, alpha = 1, family, penalty.factor)  ------------------------------ */
 /* The wrapper the reference actually calls (same lines).  foldid[n] in 1..nfolds is what
  * cv.glmnet would draw with sample(rep(seq(nfolds), length = N)); pass it explicitly
- * (validation mode) or NULL to have it drawn with R's Mersenne-Twister from `seed`
- * (rng_kind = ATE_RNG_*).  type.measure = "deviance", grouped = TRUE.
+ * (validation mode) or NULL to have it drawn with R's Mersenne-Twister (rng_kind = ATE_RNG_*):
+ * seed != 0 does set.seed(seed) first; seed == 0 continues the ctx's stream (ate_r_set_seed),
+ * the way consecutive cv.glmnet() calls share one stream in an R session.
+ * type.measure = "deviance", grouped = TRUE.
  * idx_min / idx_1se: 0-based positions of lambda.min / lambda.1se. */
 ATE_API int ate_cv_glmnet(ate_ctx *ctx, int family, long long n, int p, const double *x, const double *y,
                   const double *penalty_factor, int nfolds, const int32_t *foldid, uint32_t seed,
@@ -207,7 +209,7 @@ typedef struct ate_crossfit_opts {
     int rng_kind;       /* ATE_RNG_*                                                          */
     int on_device;      /* x_base, w, y are device pointers                                   */
     int fold_begin;     /* outer folds [fold_begin, fold_end) fitted by this call (1-based,   */
-    int fold_end;       /*   0,0 = all); rows of other folds get NaN nuisances                */
+    int fold_end;       /*   0,0 = all); rows of other folds get 0 nuisances (shards can be summed) */
     int skip_score;     /* 1: stop after the nuisances (multi-GPU drivers combine first)      */
     int shard_rank;     /* this process's rank and the number of ranks sharing ONE fit: the   */
     int shard_count;    /*   propensity paths are dealt round-robin over ranks (0,0 = no sharding) */

@@ -33,8 +33,40 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #define ORC_API __attribute__((visibility("default")))
+
+/* Thread control for the timed CPU-baseline legs of bench.py.  The composite has 2K independent
+ * cv.glmnet jobs (outer level) of nfolds independent path fits each (inner level); R itself runs
+ * all of them on one thread.  orc_set_threads(t) deals t threads over the two levels; t = 1 is the
+ * faithful single-threaded timing.  Returns the (outer * inner) thread count in effect. */
+static int g_outer_threads = 0, g_inner_threads = 1; /* 0: OpenMP's default at the outer level */
+ORC_API int orc_set_threads(int t) {
+#ifdef _OPENMP
+    if (t < 1) t = 1;
+    g_outer_threads = t < 10 ? t : 10;
+    g_inner_threads = t / g_outer_threads;
+    if (g_inner_threads < 1) g_inner_threads = 1;
+    if (g_inner_threads > 10) g_inner_threads = 10;
+    omp_set_max_active_levels(g_inner_threads > 1 ? 2 : 1);
+    omp_set_dynamic(0);
+    omp_set_num_threads(g_outer_threads);
+    return g_outer_threads * g_inner_threads;
+#else
+    (void)t;
+    return 1;
+#endif
+}
+ORC_API int orc_get_threads(void) {
+#ifdef _OPENMP
+    return (g_outer_threads > 0 ? g_outer_threads : omp_get_max_threads()) * g_inner_threads;
+#else
+    return 1;
+#endif
+}
 
 /* glmnet.control() internal constants */
 #define G_FDEV 1.0e-5
@@ -951,7 +983,12 @@ ORC_API int orc_cv_glmnet(int family, long n, int p, const double *x, const doub
     double *wk = (double *)calloc(nfolds, sizeof(double));
     int *nlk = (int *)calloc(nfolds, sizeof(int));
     int worst = 0;
-#pragma omp parallel for schedule(dynamic, 1)
+#ifdef _OPENMP
+    const int cv_threads = omp_in_parallel() ? g_inner_threads : (g_outer_threads > 0 ? g_outer_threads * g_inner_threads : omp_get_max_threads());
+#else
+    const int cv_threads = 1;
+#endif
+#pragma omp parallel for schedule(dynamic, 1) num_threads(cv_threads)
     for (int f = 1; f <= nfolds; ++f) {
         long nin_ = 0;
         for (long i = 0; i < n; ++i) nin_ += (foldid[i] == f);
@@ -1104,7 +1141,12 @@ ORC_API double orc_tau_hat_dr_est(long n, const double *w, const double *y, cons
 ORC_API double orc_bootstrap_idx(long n, const double *w, const double *y, const double *p,
                                  const double *m0, const double *m1, const int32_t *idx, int B,
                                  double *boot) {
-#pragma omp parallel for schedule(static)
+#ifdef _OPENMP
+    const int bt = g_outer_threads > 0 ? g_outer_threads * g_inner_threads : omp_get_max_threads();
+#else
+    const int bt = 1;
+#endif
+#pragma omp parallel for schedule(static) num_threads(bt)
     for (int b = 0; b < B; ++b)
         boot[b] = orc_tau_hat_dr_est(n, w, y, p, m0, m1, idx + (size_t)b * n);
     return orc_r_sd(boot, B);

@@ -60,6 +60,16 @@ def _v(a):
     return None if a is None else np.ascontiguousarray(np.asarray(a, dtype=np.float64).ravel())
 
 
+def set_threads(t: int) -> int:
+    """Deal `t` OpenMP threads over the composite's two levels of independent path fits (1 = what
+    R does).  Returns the thread count in effect.  Only bench.py's timed CPU legs call this."""
+    return int(lib().orc_set_threads(C.c_int(int(t))))
+
+
+def get_threads() -> int:
+    return int(lib().orc_get_threads())
+
+
 # ---------------------------------------------------------------- base R numerics
 def r_mean(x):
     x = _v(x)

@@ -11,6 +11,8 @@ ate_ctx <- function(device = 0L) {
   # cv.glmnet draws foldid = sample(rep(seq(nfolds), length = N)) from R's RNG; do it here so the
   # global stream advances exactly as with glmnet, then hand the ids down (validation mode)
   if (is.null(foldid)) foldid <- sample(rep(seq(nfolds), length = nrow(x)))
+  storage.mode(x) <- "double"            # as.matrix() of all-integer covariates is an integer matrix
+  if (!is.null(penalty.factor)) penalty.factor <- as.double(penalty.factor)
   m <- .Call("C_ate_cv_glmnet", ate_ctx(), as.integer(family), x, as.double(y), penalty.factor,
              as.integer(max(foldid)), as.integer(foldid), 0L)
   k <- seq_len(m$lmu)                    # the buffers hold nlambda = 100 slots; the path may stop earlier
@@ -43,7 +45,8 @@ prop_score_lasso <- function(dataset, treatment_var) {
   x <- as.matrix(dataset[covariates]); w <- as.matrix(dataset[, treatment_var])
   model <- .cv_glmnet_b200(x, w, 1L)
   s <- model$idx.1se
-  .Call("C_ate_predict", ate_ctx(), x, model$a0[s], model$beta[, s], TRUE)   # n x 1 matrix
+  storage.mode(x) <- "double"
+  .Call("C_ate_predict", ate_ctx(), x, model$a0[s], as.double(model$beta[, s]), TRUE)   # n x 1 matrix
 }
 
 # ate_functions.R:267-283
@@ -54,7 +57,10 @@ tau_hat_dr_est <- function(w, y, p, tauhat0x, tauhat1x) {
 }
 
 # ate_functions.R:241-263 (the tail of doubly_robust / doubly_robust_glm; nuisances as today)
+# boot_idx (validation mode): integer matrix n x B, ONE REPLICATE PER COLUMN -- column b is the
+# sample(n, n, replace = T) of replicate b, i.e. cbind() of the draws in loop order; values in 1..n
 .dr_tail <- function(w, y, p, tauhat0x, tauhat1x, bootstrap_se, method, B = 1000, boot_idx = NULL) {
+  if (!is.null(boot_idx)) { d <- dim(boot_idx); boot_idx <- as.integer(boot_idx); dim(boot_idx) <- d }
   ts <- .Call("C_ate_aipw_score", ate_ctx(), as.double(w), as.double(y), as.double(p),
               as.double(tauhat0x), as.double(tauhat1x))
   tau_hat <- ts[1]
@@ -78,6 +84,8 @@ tau_hat_dr_est <- function(w, y, p, tauhat0x, tauhat1x) {
 
 # lm() %>% summary() %>% coef() for the regression estimators: rows named like R names them
 .lm_b200 <- function(x, y, weights = NULL, resid = FALSE) {
+  storage.mode(x) <- "double"
+  if (!is.null(weights)) weights <- as.double(weights)
   tab <- .Call("C_ate_lm", ate_ctx(), x, as.double(y), weights, resid)
   dimnames(tab) <- list(c("(Intercept)", colnames(x)), c("Estimate", "Std. Error"))
   tab
@@ -112,7 +120,8 @@ prop_score_ols <- function(dataset, p, treatment_var, outcome_var, method = "Pro
 
 # ate_functions.R:286-328 -- expansion, both cv.glmnet fits and the post-lasso OLS on the library
 belloni <- function(dataset, treatment_var, outcome_var, method = "Belloni et.al") {
-  x <- .Call("C_ate_expand_deg2", ate_ctx(), as.matrix(dataset[, covariates]))            # :288-296 (mains, then products)
+  x0 <- as.matrix(dataset[, covariates]); storage.mode(x0) <- "double"
+  x <- .Call("C_ate_expand_deg2", ate_ctx(), x0)                                          # :288-296 (mains, then products)
   w <- as.matrix(dataset[treatment_var]); y <- as.matrix(dataset[outcome_var])
   model_xw <- .cv_glmnet_b200(x, w, 0L); model_xy <- .cv_glmnet_b200(x, y, 0L)            # :304-305
   s <- model_xw$lambda[model_xw$idx.min]
@@ -127,8 +136,8 @@ belloni <- function(dataset, treatment_var, outcome_var, method = "Belloni et.al
 # ate_functions.R:211-264 -- same formals; only the two glm() calls and the tail change
 doubly_robust_glm <- function(dataset, treatment_var, outcome_var, bootstrap_se = F) {
   mm <- function(d) model.matrix(~ ., d)[, -1, drop = FALSE]          # what glm builds for `~ .`
-  plogis_lin <- function(x, b) .Call("C_ate_predict", ate_ctx(), x, b[1], b[-1], TRUE)
-  xo <- mm(dataset[, names(dataset) != outcome_var])
+  plogis_lin <- function(x, b) .Call("C_ate_predict", ate_ctx(), x, b[1], as.double(b[-1]), TRUE)
+  xo <- mm(dataset[, names(dataset) != outcome_var]); storage.mode(xo) <- "double"
   condmean <- .Call("C_ate_glm_binomial", ate_ctx(), xo, as.double(dataset[, outcome_var]))      # :218-220
   x1 <- xo; x1[, treatment_var] <- 1; x0 <- xo; x0[, treatment_var] <- 0                       # :221-226
   tauhat1x <- plogis_lin(x1, condmean); tauhat0x <- plogis_lin(x0, condmean)                   # :227-228
@@ -143,7 +152,10 @@ doubly_robust_glm <- function(dataset, treatment_var, outcome_var, bootstrap_se 
 crossfit_aipw <- function(dataset, treatment_var, outcome_var, bootstrap_se = T, B = 1000, K = 5,
                           seed = 1991, foldid = NULL, inner_ps = NULL, inner_out = NULL, boot_idx = NULL,
                           expand = 0L, n_continuous = 0L) {
-  x <- as.matrix(dataset[covariates])
+  x <- as.matrix(dataset[covariates]); storage.mode(x) <- "double"
+  asint <- function(m) if (is.null(m)) NULL else { d <- dim(m); m <- as.integer(m); dim(m) <- d; m }
+  foldid <- asint(foldid); inner_ps <- asint(inner_ps); inner_out <- asint(inner_out)
+  boot_idx <- asint(boot_idx)            # n x B, one replicate per column (see .dr_tail)
   r <- .Call("C_ate_crossfit_aipw", ate_ctx(), x, as.double(dataset[, treatment_var]),
              as.double(dataset[, outcome_var]), as.integer(K), as.integer(if (bootstrap_se) B else 0L),
              as.integer(seed), foldid, inner_ps, inner_out, boot_idx, as.integer(expand), as.integer(n_continuous))
