@@ -42,7 +42,8 @@ class CrossfitResult(C.Structure):
         ("rounds_irls", C.c_int), ("gram_launches", c_ll), ("ms_design", C.c_double),
         ("ms_outcome", C.c_double), ("ms_propensity", C.c_double), ("ms_score", C.c_double),
         ("ms_bootstrap", C.c_double), ("irls_solves", C.c_double), ("strong_mean", C.c_double),
-        ("strong_frac2", C.c_double),
+        ("strong_frac2", C.c_double), ("ms_folds", C.c_double), ("step_launches", C.c_double),
+        ("row_fits", C.c_double), ("rows_staged", C.c_double), ("list_misses", C.c_double),
     ]
 
 
@@ -57,6 +58,9 @@ SIGNATURES = {
     "ate_last_error": (C.c_char_p, [_vp]),
     "ate_ctx_stream": (_vp, [_vp]),
     "ate_ctx_set_allreduce": (C.c_int, [_vp, _vp, _vp]),
+    "ate_nccl_unique_id": (C.c_int, [_vp]),
+    "ate_ctx_nccl_init": (C.c_int, [_vp, _vp, C.c_int, C.c_int]),
+    "ate_ctx_nccl_destroy": (C.c_int, [_vp]),
     "ate_launch_count": (c_ll, [_vp]),
     "ate_profile_enable": (C.c_int, [_vp, C.c_int]),
     "ate_profile_read": (C.c_int, [_vp, c_dp, C.POINTER(c_ll), c_dp, c_dp]),
@@ -69,6 +73,9 @@ SIGNATURES = {
                                 C.c_uint32, C.c_int, C.c_int, C.c_double, C.c_int,
                                 C.POINTER(C.c_int), _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int),
                                 C.POINTER(C.c_int), _vp, C.POINTER(C.c_int)]),
+    "ate_cv_glmnet_device": (C.c_int, [_vp, C.c_int, c_ll, C.c_int, _vp, c_ll, _vp, C.c_int, _vp, C.c_int,
+                                       C.c_double, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), _vp, _vp, _vp,
+                                       _vp, _vp, C.POINTER(C.c_int), C.POINTER(C.c_int), _vp, C.POINTER(C.c_int)]),
     "ate_glm_binomial": (C.c_int, [_vp, c_ll, C.c_int, _vp, _vp, C.c_int, C.c_double, _vp, c_dp,
                                    C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "ate_lm": (C.c_int, [_vp, c_ll, C.c_int, _vp, _vp, _vp, _vp, _vp, c_dp, c_dp, C.POINTER(C.c_int),
@@ -88,7 +95,7 @@ SIGNATURES = {
                                     C.POINTER(CrossfitResult)]),
     "ate_cv_select": (C.c_int, [C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int),
                                 C.POINTER(C.c_int)]),
-    "ate_step_plan_describe": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), _vp]),
+    "ate_round_plan_describe": (C.c_int, [C.c_int, _vp, C.c_int, C.c_int, _vp]),
     "ate_weighted_gram": (C.c_int, [_vp, c_ll, C.c_int, _vp, c_ll, _vp, _vp, c_ll, _vp, C.c_int]),
 }
 

@@ -11,6 +11,8 @@
 //                    replicate depends only on (seed, replicate id).
 #include <math.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace {
@@ -53,28 +55,60 @@ __device__ __forceinline__ void take(const double *__restrict__ t1, const double
     }
 }
 
-// MODE 0: index matrix, MODE 1: Philox
+// one validated gather: a 1-based index outside 1..n (R would give NA for it) raises the flag and
+// contributes nothing
+template <bool TWO_TABLES>
+__device__ __forceinline__ void take_checked(const double *__restrict__ t1, const double *__restrict__ t2, int idx1,
+                                             long long n, double &s1, double &c1, double &s2, int &bad) {
+    const long long i = (long long)idx1 - 1;
+    if (i < 0 || i >= n)
+        bad = 1;
+    else
+        take<TWO_TABLES>(t1, t2, i, s1, c1, s2);
+}
+
+// MODE 0: index matrix (HBM-bound: the B x n int32 stream is read once, 16 bytes per load where the
+// replicate's row is 16-byte aligned; the score tables are L2-resident), MODE 1: Philox
 template <int MODE, bool TWO_TABLES>
 __global__ void __launch_bounds__(BOOT_THREADS)
 bootstrap_kernel(long long n, const double *__restrict__ t1, const double *__restrict__ t2,
                  const int32_t *__restrict__ idx, uint64_t seed, long long rep0,
-                 double *__restrict__ boot) {
+                 double *__restrict__ boot, int *__restrict__ bad_flag) {
     __shared__ double red[3 * 32];
     const long long rep = rep0 + blockIdx.x;
     double acc[3] = {0.0, 0.0, 0.0};
     if (MODE == 0) {
         const int32_t *row = idx + (size_t)blockIdx.x * (size_t)n;
-        long long t = threadIdx.x;
-        // 4 independent gathers in flight per thread
-        for (; t + 3LL * BOOT_THREADS < n; t += 4LL * BOOT_THREADS) {
-            const int i0 = __ldg(row + t), i1 = __ldg(row + t + BOOT_THREADS);
-            const int i2 = __ldg(row + t + 2 * BOOT_THREADS), i3 = __ldg(row + t + 3 * BOOT_THREADS);
-            take<TWO_TABLES>(t1, t2, i0 - 1, acc[0], acc[1], acc[2]);
-            take<TWO_TABLES>(t1, t2, i1 - 1, acc[0], acc[1], acc[2]);
-            take<TWO_TABLES>(t1, t2, i2 - 1, acc[0], acc[1], acc[2]);
-            take<TWO_TABLES>(t1, t2, i3 - 1, acc[0], acc[1], acc[2]);
+        int bad = 0;
+        // peel to a 16-byte boundary, then int4 loads (two in flight per thread), then the tail
+        long long head = (long long)(((16 - ((uintptr_t)row & 15)) & 15) >> 2);
+        if (head > n) head = n;
+        for (long long t = threadIdx.x; t < head; t += BOOT_THREADS)
+            take_checked<TWO_TABLES>(t1, t2, __ldg(row + t), n, acc[0], acc[1], acc[2], bad);
+        const int4 *row4 = reinterpret_cast<const int4 *>(row + head);
+        const long long n4 = (n - head) >> 2;
+        long long q = threadIdx.x;
+        for (; q + BOOT_THREADS < n4; q += 2LL * BOOT_THREADS) {
+            const int4 a = __ldg(row4 + q), b = __ldg(row4 + q + BOOT_THREADS);
+            take_checked<TWO_TABLES>(t1, t2, a.x, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, a.y, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, a.z, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, a.w, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, b.x, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, b.y, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, b.z, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, b.w, n, acc[0], acc[1], acc[2], bad);
         }
-        for (; t < n; t += BOOT_THREADS) take<TWO_TABLES>(t1, t2, __ldg(row + t) - 1, acc[0], acc[1], acc[2]);
+        for (; q < n4; q += BOOT_THREADS) {
+            const int4 a = __ldg(row4 + q);
+            take_checked<TWO_TABLES>(t1, t2, a.x, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, a.y, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, a.z, n, acc[0], acc[1], acc[2], bad);
+            take_checked<TWO_TABLES>(t1, t2, a.w, n, acc[0], acc[1], acc[2], bad);
+        }
+        for (long long t = head + 4 * n4 + threadIdx.x; t < n; t += BOOT_THREADS)
+            take_checked<TWO_TABLES>(t1, t2, __ldg(row + t), n, acc[0], acc[1], acc[2], bad);
+        if (bad) atomicOr(bad_flag, 1);
     } else {
         const long long npairs = (n + 1) >> 1;
         const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
@@ -113,38 +147,92 @@ __global__ void psi_sum_kernel(long long n, const double *__restrict__ e1,
 
 }  // namespace
 
-// d_est1/d_est2/d_idx are device pointers; boot_host[B] is a host buffer.
+// d_est1 / d_est2: device score tables.  idx (index mode): the B x n matrix of 1-based indices, on the
+// device, or on the host (idx_on_host) in which case it is streamed through two device blocks of
+// <= 256 MB, the upload of one overlapping the kernel on the other -- the matrix (8 GB at C1, 40 GB at
+// C2) is never resident as a whole.  Results: d_out (device, optional) and boot_host (host, optional).
+// Index mode validates every index: one outside 1..n fails the call.
+// d_psi (optional): est1 + est2 as the score kernel already wrote it, with has_nan_known = whether any
+// est1 is NaN; without it one extra pass builds the table here.
 int ate_i_bootstrap(ate_ctx *ctx, long long n, const double *d_est1, const double *d_est2, int B,
-                    int mode, const int32_t *d_idx, uint64_t seed, long long rep_offset,
-                    double *boot_host) {
+                    int mode, const int32_t *idx, int idx_on_host, uint64_t seed, long long rep_offset,
+                    double *d_out, double *boot_host, const double *d_psi, int has_nan_known) {
     if (B <= 0) return 0;
-    if (mode == ATE_BOOT_INDEX && !d_idx) return ate_fail(ctx, -1, "bootstrap: index mode needs idx");
-    DevBuf<double> psi, dboot;
-    DevBuf<unsigned int> flag;
-    ATE_CUDA(ctx, psi.alloc((size_t)n));
-    ATE_CUDA(ctx, dboot.alloc((size_t)B));
-    ATE_CUDA(ctx, flag.alloc(1));
-    ATE_CUDA(ctx, cudaMemsetAsync(flag.p, 0, sizeof(unsigned int), ctx->stream));
-    int blocks = ctx->num_sms * 4;
-    psi_sum_kernel<<<blocks, 256, 0, ctx->stream>>>(n, d_est1, d_est2, psi.p, flag.p);
-    ATE_LAUNCHED(ctx);
+    if (mode == ATE_BOOT_INDEX && !idx) return ate_fail(ctx, -1, "bootstrap: index mode needs idx");
+    void *blk = nullptr;
+    ATE_TRY(ate_cached(ctx, "boot.state", sizeof(double) * ((size_t)n + (size_t)B) + 256, &blk));
+    double *psi_own = (double *)blk, *dboot = psi_own + n;
+    unsigned int *flag = (unsigned int *)(dboot + B);
+    int *bad = (int *)(flag + 1);
+    ATE_CUDA(ctx, cudaMemsetAsync(flag, 0, 2 * sizeof(int), ctx->stream));
     unsigned int has_nan = 0;
-    ATE_CUDA(ctx, cudaMemcpyAsync(&has_nan, flag.p, sizeof(has_nan), cudaMemcpyDeviceToHost, ctx->stream));
-    ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (mode == ATE_BOOT_INDEX) {
-        if (has_nan)
-            bootstrap_kernel<0, true><<<B, BOOT_THREADS, 0, ctx->stream>>>(n, d_est1, d_est2, d_idx, seed, rep_offset, dboot.p);
-        else
-            bootstrap_kernel<0, false><<<B, BOOT_THREADS, 0, ctx->stream>>>(n, psi.p, nullptr, d_idx, seed, rep_offset, dboot.p);
+    const double *psi = d_psi;
+    if (d_psi) {
+        has_nan = has_nan_known ? 1u : 0u;
     } else {
-        if (has_nan)
-            bootstrap_kernel<1, true><<<B, BOOT_THREADS, 0, ctx->stream>>>(n, d_est1, d_est2, nullptr, seed, rep_offset, dboot.p);
-        else
-            bootstrap_kernel<1, false><<<B, BOOT_THREADS, 0, ctx->stream>>>(n, psi.p, nullptr, nullptr, seed, rep_offset, dboot.p);
+        psi_sum_kernel<<<ctx->num_sms * 4, 256, 0, ctx->stream>>>(n, d_est1, d_est2, psi_own, flag);
+        ATE_LAUNCHED(ctx);
+        ATE_CUDA(ctx, cudaMemcpyAsync(&has_nan, flag, sizeof(has_nan), cudaMemcpyDeviceToHost, ctx->stream));
+        ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        psi = psi_own;
     }
-    ATE_LAUNCHED(ctx);
-    ATE_CUDA(ctx, cudaMemcpyAsync(boot_host, dboot.p, sizeof(double) * (size_t)B, cudaMemcpyDeviceToHost, ctx->stream));
+    auto launch = [&](int nb, const int32_t *didx, long long rep0, double *out, cudaStream_t st) {
+        if (mode == ATE_BOOT_INDEX) {
+            if (has_nan)
+                bootstrap_kernel<0, true><<<nb, BOOT_THREADS, 0, st>>>(n, d_est1, d_est2, didx, seed, rep0, out, bad);
+            else
+                bootstrap_kernel<0, false><<<nb, BOOT_THREADS, 0, st>>>(n, psi, nullptr, didx, seed, rep0, out, bad);
+        } else {
+            if (has_nan)
+                bootstrap_kernel<1, true><<<nb, BOOT_THREADS, 0, st>>>(n, d_est1, d_est2, nullptr, seed, rep0, out, bad);
+            else
+                bootstrap_kernel<1, false><<<nb, BOOT_THREADS, 0, st>>>(n, psi, nullptr, nullptr, seed, rep0, out, bad);
+        }
+    };
+    if (mode == ATE_BOOT_INDEX && idx_on_host) {
+        long long per = (256LL << 20) / (4 * n);
+        if (per < 1) per = 1;
+        if (per > B) per = B;
+        void *ib = nullptr;
+        ATE_TRY(ate_cached(ctx, "boot.idx", sizeof(int32_t) * (size_t)n * (size_t)per * 2, &ib));
+        int32_t *dblk[2] = {(int32_t *)ib, (int32_t *)ib + (size_t)n * per};
+        cudaStream_t cs = nullptr;
+        cudaEvent_t up[2] = {nullptr, nullptr}, used[2] = {nullptr, nullptr};
+        ATE_CUDA(ctx, cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; ++k) {
+            cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&used[k], cudaEventDisableTiming);
+        }
+        int rc = 0, turn = 0;
+        for (long long b0 = 0; b0 < B && rc == 0; b0 += per, turn ^= 1) {
+            const int nb = (int)std::min<long long>(per, B - b0);
+            if (b0 >= 2 * per) cudaStreamWaitEvent(cs, used[turn], 0);  // the kernel that read this block is done
+            if (cudaMemcpyAsync(dblk[turn], idx + (size_t)b0 * (size_t)n, sizeof(int32_t) * (size_t)n * nb, cudaMemcpyHostToDevice, cs) != cudaSuccess) rc = -1;
+            cudaEventRecord(up[turn], cs);
+            cudaStreamWaitEvent(ctx->stream, up[turn], 0);
+            launch(nb, dblk[turn], rep_offset + b0, dboot + b0, ctx->stream);
+            ctx->launches++;
+            if (cudaGetLastError() != cudaSuccess) rc = -1;
+            cudaEventRecord(used[turn], ctx->stream);
+        }
+        cudaStreamSynchronize(cs);
+        cudaStreamSynchronize(ctx->stream);
+        for (int k = 0; k < 2; ++k) {
+            cudaEventDestroy(up[k]);
+            cudaEventDestroy(used[k]);
+        }
+        cudaStreamDestroy(cs);
+        if (rc != 0) return ate_fail(ctx, -100, "bootstrap: streaming the index matrix failed");
+    } else {
+        launch(B, idx, rep_offset, dboot, ctx->stream);
+        ATE_LAUNCHED(ctx);
+    }
+    int hbad = 0;
+    if (mode == ATE_BOOT_INDEX) ATE_CUDA(ctx, cudaMemcpyAsync(&hbad, bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (d_out) ATE_CUDA(ctx, cudaMemcpyAsync(d_out, dboot, sizeof(double) * (size_t)B, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (boot_host) ATE_CUDA(ctx, cudaMemcpyAsync(boot_host, dboot, sizeof(double) * (size_t)B, cudaMemcpyDeviceToHost, ctx->stream));
     ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (hbad) return ate_fail(ctx, -1, "bootstrap: an index lies outside 1..%lld (R's sample() never produces one; NA_integer_ is not accepted)", n);
     return 0;
 }
 
@@ -161,26 +249,20 @@ extern "C" int ate_bootstrap(ate_ctx *ctx, long long n, const double *w, const d
         return ate_fail(ctx, -1, "ate_bootstrap: ATE_BOOT_INDEX needs the B x n index matrix");
     ATE_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t N = (size_t)n;
-    DevBuf<double> d, e;
-    DevBuf<int32_t> di;
+    void *blk = nullptr;
+    ATE_TRY(ate_cached(ctx, "boot.inputs", sizeof(double) * N * 7, &blk));
+    double *d = (double *)blk, *e = d + 5 * N;
     const double *dw = w, *dy = y, *dp = p, *d0 = m0, *d1 = m1;
-    const int32_t *didx = idx;
     if (!on_device) {
-        ATE_CUDA(ctx, d.alloc(N * 5));
         const double *src[5] = {w, y, p, m0, m1};
         for (int k = 0; k < 5; ++k)
-            ATE_CUDA(ctx, cudaMemcpyAsync(d.p + k * N, src[k], N * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-        dw = d.p; dy = d.p + N; dp = d.p + 2 * N; d0 = d.p + 3 * N; d1 = d.p + 4 * N;
-        if (mode == ATE_BOOT_INDEX) {
-            ATE_CUDA(ctx, di.alloc(N * (size_t)B));
-            ATE_CUDA(ctx, cudaMemcpyAsync(di.p, idx, N * (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
-            didx = di.p;
-        }
+            ATE_CUDA(ctx, cudaMemcpyAsync(d + k * N, src[k], N * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        dw = d; dy = d + N; dp = d + 2 * N; d0 = d + 3 * N; d1 = d + 4 * N;
     }
-    ATE_CUDA(ctx, e.alloc(N * 2));
     double tau, se0;
-    ATE_TRY(ate_i_score(ctx, n, dw, dy, dp, d0, d1, e.p, e.p + N, &tau, &se0));
-    ATE_TRY(ate_i_bootstrap(ctx, n, e.p, e.p + N, B, mode, didx, seed, rep_offset, boot));
+    ATE_TRY(ate_i_score(ctx, n, dw, dy, dp, d0, d1, e, e + N, &tau, &se0));
+    // boot is a host buffer in both modes
+    ATE_TRY(ate_i_bootstrap(ctx, n, e, e + N, B, mode, idx, !on_device, seed, rep_offset, nullptr, boot, nullptr, 0));
     if (se) *se = ate_host_sd(boot, B);
     return 0;
 }

@@ -25,8 +25,8 @@ struct ate_ctx {
     cudaStream_t stream = nullptr;
     std::string err;
     long long launches = 0;
-    // profiling of the dominant kernel (weighted Gram)
-    bool profile = false;
+    // per-launch CUDA-event timing: bit 1 = the IRLS step kernel (irls_round.cu), bit 2 = the Gram kernel
+    int profile = 0;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
     std::vector<std::pair<int, long long>> prof_shape;  // (columns in the Gram, rows) per timed launch
     double prof_flops = 0.0, prof_bytes = 0.0;
@@ -40,9 +40,13 @@ struct ate_ctx {
     ate_rng_state rng;
     // large work buffers kept across calls (cudaMalloc/cudaFree of multi-GB blocks cost ~1 s per fit)
     std::map<std::string, std::pair<void *, size_t>> cache;
+    std::map<std::string, std::pair<void *, size_t>> pinned;  // page-locked host staging, same lifetime
     // multi-GPU: host-buffer sum over the ranks that share one fit
     ate_allreduce_fn allreduce = nullptr;
     void *allreduce_user = nullptr;
+    // multi-GPU: NCCL communicator owned by the ctx (comm.cu); collectives run on `stream`
+    void *nccl_comm = nullptr;
+    int nccl_rank = 0, nccl_nranks = 1;
 };
 
 // ---- error handling ------------------------------------------------------------------
@@ -103,6 +107,8 @@ int ate_scratch(ate_ctx *ctx, size_t bytes, void **out);
 // persistent, grow-only buffer identified by `tag`; released by ate_ctx_destroy
 int ate_cached(ate_ctx *ctx, const char *tag, size_t bytes, void **out);
 int ate_gram_scratch(ate_ctx *ctx, size_t bytes, void **out);
+// persistent, grow-only page-locked HOST buffer (contents are lost when it grows)
+int ate_cached_pinned(ate_ctx *ctx, const char *tag, size_t bytes, void **out);
 
 // ---- device helpers ---------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {
@@ -138,21 +144,24 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
                long long row_begin, long long nrows, const double *v, double *G /*p*p*/,
                long long hole_begin = 0, long long hole_len = 0, const int *colidx = nullptr,
                int ncload = 0, int ldg = 0);
+// fold the row-chunk partials of a block-lower-triangular Gram into G (both triangles)
+int ate_i_gram_fold(ate_ctx *ctx, const double *partials, int nchunks, int nblk, int p, int ldg, double *G);
 int ate_i_transpose_to_rowmajor(ate_ctx *ctx, const double *x_colmajor, long long n, int p,
                                 double *X, long long ld, int col_offset);
 int ate_i_standardize(ate_ctx *ctx, double *d_x, long long n, int p, const int *d_cols, int ncols,
                       double *d_center, double *d_scale);
-int ate_i_build_design(ate_ctx *ctx, const double *d_xbase, long long n, int p0, int expand,
+// d_xbase: column-major base covariates with leading dimension ldx (>= n rows are built from its top)
+int ate_i_build_design(ate_ctx *ctx, const double *d_xbase, long long ldx, long long n, int p0, int expand,
                        const double *d_w, const double *d_y, double *d_X, long long ld);
 int ate_i_gather_rows(ate_ctx *ctx, const double *X, long long ld, const int32_t *list, long long nt,
                       int ncs, double *Xp, long long ldp);
 int ate_i_fill_column(ate_ctx *ctx, double *X, long long n, long long ld, int col, double value);
 int ate_i_score(ate_ctx *ctx, long long n, const double *w, const double *y, const double *p,
                 const double *m0, const double *m1, double *d_est1, double *d_est2,
-                double *tau, double *se);
+                double *tau, double *se, double *d_psi = nullptr, double *n_ok = nullptr);
 int ate_i_bootstrap(ate_ctx *ctx, long long n, const double *d_est1, const double *d_est2, int B,
-                    int mode, const int32_t *d_idx, uint64_t seed, long long rep_offset,
-                    double *boot_host);
+                    int mode, const int32_t *idx, int idx_on_host, uint64_t seed, long long rep_offset,
+                    double *d_out, double *boot_host, const double *d_psi, int has_nan_known);
 double ate_host_sd(const double *x, long long n);
 void ate_host_rng_seed(ate_rng_state *r, uint32_t seed);
 void ate_host_sample_replace(ate_rng_state *r, int n, long long k, int kind, int32_t *out);

@@ -50,12 +50,15 @@ extern "C" void ate_ctx_destroy(ate_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    ate_ctx_nccl_destroy(ctx);
     for (auto &pr : ctx->prof_events) {
         cudaEventDestroy(pr.first);
         cudaEventDestroy(pr.second);
     }
     for (auto &kv : ctx->cache)
         if (kv.second.first) cudaFree(kv.second.first);
+    for (auto &kv : ctx->pinned)
+        if (kv.second.first) cudaFreeHost(kv.second.first);
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->gram_scratch) cudaFree(ctx->gram_scratch);
     cudaStreamDestroy(ctx->stream);
@@ -88,7 +91,7 @@ extern "C" int ate_profile_enable(ate_ctx *ctx, int on) {
     ctx->prof_shape.clear();
     ctx->prof_flops = ctx->prof_bytes = 0.0;
     ctx->prof_launches = 0;
-    ctx->profile = on != 0;
+    ctx->profile = on < 0 ? 0 : (on & 3);
     return 0;
 }
 
@@ -139,6 +142,21 @@ static int grow(ate_ctx *ctx, void **buf, size_t *have, size_t want, void **out)
 int ate_cached(ate_ctx *ctx, const char *tag, size_t bytes, void **out) {
     auto &slot = ctx->cache[tag];
     return grow(ctx, &slot.first, &slot.second, bytes, out);
+}
+
+int ate_cached_pinned(ate_ctx *ctx, const char *tag, size_t bytes, void **out) {
+    auto &slot = ctx->pinned[tag];
+    if (bytes > slot.second) {
+        ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (slot.first) ATE_CUDA(ctx, cudaFreeHost(slot.first));
+        slot.first = nullptr;
+        slot.second = 0;
+        const size_t cap = bytes + (bytes >> 2) + 4096;
+        ATE_CUDA(ctx, cudaHostAlloc(&slot.first, cap, cudaHostAllocDefault));
+        slot.second = cap;
+    }
+    *out = slot.first;
+    return 0;
 }
 
 int ate_scratch(ate_ctx *ctx, size_t bytes, void **out) {

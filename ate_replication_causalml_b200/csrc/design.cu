@@ -19,7 +19,9 @@ namespace {
 
 constexpr int MOM_THREADS = 256;
 
-// partial shifted moments of column cols[blockIdx.y]; shift = first element of the column
+// partial shifted moments of column cols[blockIdx.y]; shift = first element of the column.
+// The column is walked in 16-byte pairs from its first 16-byte-aligned element; the (at most one)
+// element before it and the odd tail are handled by block 0 / the last pair's owner.
 __global__ void __launch_bounds__(MOM_THREADS)
 col_moments_kernel(const double *__restrict__ x, long long n, const int *__restrict__ cols,
                    double *__restrict__ partials /*[ncols][gridDim.x][2]*/) {
@@ -28,11 +30,27 @@ col_moments_kernel(const double *__restrict__ x, long long n, const int *__restr
     const double *xj = x + (size_t)j * (size_t)n;
     const double c = __ldg(xj);
     double acc[2] = {0.0, 0.0};
+    const long long head = (long long)(((uintptr_t)xj >> 3) & 1);  // elements before the aligned body
+    const double2 *x2 = reinterpret_cast<const double2 *>(xj + head);
+    const long long n2 = (n - head) >> 1;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const double d = __ldg(xj + i) - c;
-        acc[0] += d;
-        acc[1] += d * d;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+        const double2 v = __ldg(x2 + i);
+        const double d0 = v.x - c, d1 = v.y - c;
+        acc[0] += d0 + d1;
+        acc[1] += d0 * d0 + d1 * d1;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (head) {
+            const double d = __ldg(xj) - c;
+            acc[0] += d;
+            acc[1] += d * d;
+        }
+        if (head + 2 * n2 < n) {
+            const double d = __ldg(xj + n - 1) - c;
+            acc[0] += d;
+            acc[1] += d * d;
+        }
     }
     block_sum<2>(acc, red);
     if (threadIdx.x == 0) {
@@ -64,16 +82,27 @@ __global__ void col_moments_finish_kernel(const double *__restrict__ x, long lon
     scale[cidx] = sqrt(ssc / (dn - 1.0));
 }
 
-__global__ void col_apply_kernel(double *__restrict__ x, long long n, const int *__restrict__ cols,
-                                 const double *__restrict__ center,
-                                 const double *__restrict__ scale) {
+__global__ void __launch_bounds__(MOM_THREADS)
+col_apply_kernel(double *__restrict__ x, long long n, const int *__restrict__ cols,
+                 const double *__restrict__ center, const double *__restrict__ scale) {
     const int cidx = blockIdx.y;
     const int j = cols ? cols[cidx] : cidx;
     double *xj = x + (size_t)j * (size_t)n;
     const double mu = center[cidx], sd = scale[cidx];
+    const long long head = (long long)(((uintptr_t)xj >> 3) & 1);
+    double2 *x2 = reinterpret_cast<double2 *>(xj + head);
+    const long long n2 = (n - head) >> 1;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-        xj[i] = (xj[i] - mu) / sd;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+        double2 v = x2[i];
+        v.x = (v.x - mu) / sd;
+        v.y = (v.y - mu) / sd;
+        x2[i] = v;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (head) xj[0] = (xj[0] - mu) / sd;
+        if (head + 2 * n2 < n) xj[n - 1] = (xj[n - 1] - mu) / sd;
+    }
 }
 
 // ---- expansion, col-major in -> col-major out (public ate_expand_deg2) ----------------------
@@ -85,74 +114,110 @@ expand_colmajor_kernel(const double *__restrict__ x, long long n, int p0, int in
     extern __shared__ double tile[];  // [p0][EXP_ROWS]
     const long long r0 = (long long)blockIdx.x * EXP_ROWS;
     const int rows = (int)((n - r0) < EXP_ROWS ? (n - r0) : EXP_ROWS);
-    for (int e = threadIdx.x; e < p0 * EXP_ROWS; e += blockDim.x) {
-        const int j = e / EXP_ROWS, r = e % EXP_ROWS;
-        tile[e] = r < rows ? __ldg(x + (size_t)j * n + r0 + r) : 0.0;
+    for (int j = threadIdx.x / EXP_ROWS; j < p0; j += 256 / EXP_ROWS) {
+        const int r = threadIdx.x % EXP_ROWS;  // powers of two: shifts
+        tile[j * EXP_ROWS + r] = r < rows ? __ldg(x + (size_t)j * n + r0 + r) : 0.0;
     }
     __syncthreads();
     const int nmain = include_main ? p0 : 0;
     const int pout = nmain + p0 * p0;
-    // consecutive threads -> consecutive rows of one output column (coalesced 8 B stores)
-    for (int e = threadIdx.x; e < pout * EXP_ROWS; e += blockDim.x) {
-        const int c = e / EXP_ROWS, r = e % EXP_ROWS;
-        if (r >= rows) continue;
-        double v;
-        if (c < nmain)
-            v = tile[c * EXP_ROWS + r];
-        else {
-            const int q = c - nmain, c1 = q / p0, c2 = q % p0;
-            v = tile[c1 * EXP_ROWS + r] * tile[c2 * EXP_ROWS + r];
+    // a thread owns a fixed pair of rows and walks the output columns; (c1, c2) advance by counters
+    constexpr int PAIRS = EXP_ROWS / 2, CSTEP = 256 / PAIRS;
+    const int rp = threadIdx.x % PAIRS, r = 2 * rp;
+    int c = threadIdx.x / PAIRS;
+    int q = c - nmain, c1 = 0, c2 = 0;
+    if (q >= 0) {
+        c1 = q / p0;  // once per thread
+        c2 = q - c1 * p0;
+    }
+    const bool vec = ((n & 1) == 0);  // every column then starts 16-byte aligned (r0 and r are even)
+    for (; c < pout; c += CSTEP) {
+        double v0, v1;
+        if (c < nmain) {
+            v0 = tile[c * EXP_ROWS + r];
+            v1 = tile[c * EXP_ROWS + r + 1];
+            if (c + CSTEP >= nmain) {  // entering the products
+                q = c + CSTEP - nmain;
+                c1 = q / p0;
+                c2 = q - c1 * p0;
+            }
+        } else {
+            v0 = tile[c1 * EXP_ROWS + r] * tile[c2 * EXP_ROWS + r];
+            v1 = tile[c1 * EXP_ROWS + r + 1] * tile[c2 * EXP_ROWS + r + 1];
+            c2 += CSTEP;
+            while (c2 >= p0) {
+                c2 -= p0;
+                ++c1;
+            }
         }
-        out[(size_t)c * n + r0 + r] = v;
+        double *o = out + (size_t)c * n + r0 + r;
+        if (vec && r + 1 < rows)
+            *reinterpret_cast<double2 *>(o) = make_double2(v0, v1);
+        else {
+            if (r < rows) o[0] = v0;
+            if (r + 1 < rows) o[1] = v1;
+        }
     }
 }
 
 // ---- design builder: col-major base (+ w, y) -> row-major design with appended columns ------
 // columns: [mains (nmain)] [products (nprod)] [w] [y] [1] [0 ... to ld]
+// Every output column is the product of two entries of the staged row [base (p0) | w | y | 1 | 0]:
+// a main is base * 1, the appended columns are w * 1, y * 1, 1 * 1, the padding 0 * 0.  The two
+// factors of each column are looked up in a table built once per block (no division per element),
+// and a thread writes two adjacent columns with one 16-byte store.
 constexpr int DES_ROWS = 32;
 
 __global__ void __launch_bounds__(256)
-build_design_kernel(const double *__restrict__ x, long long n, int p0, int nmain, int nprod,
+build_design_kernel(const double *__restrict__ x, long long ldx, long long n, int p0, int nmain, int nprod,
                     const double *__restrict__ w, const double *__restrict__ y,
                     double *__restrict__ X, long long ld) {
-    extern __shared__ double tile[];  // [DES_ROWS][p0 + 2]
-    const int tw = p0 + 2;
+    extern __shared__ double tile[];  // [p0 + 4][DES_ROWS + 1], then the factor table
+    const int tw = p0 + 4, tp = DES_ROWS + 1;
+    short2 *lut = reinterpret_cast<short2 *>(tile + (size_t)tw * tp);
     const long long r0 = (long long)blockIdx.x * DES_ROWS;
     const int rows = (int)((n - r0) < DES_ROWS ? (n - r0) : DES_ROWS);
     for (int e = threadIdx.x; e < tw * DES_ROWS; e += blockDim.x) {
         const int j = e / DES_ROWS, r = e % DES_ROWS;  // consecutive threads -> consecutive rows
         double v = 0.0;
-        if (r < rows) {
+        if (j == p0 + 2)
+            v = 1.0;
+        else if (r < rows && j < p0 + 2) {
             if (j < p0)
-                v = __ldg(x + (size_t)j * n + r0 + r);
+                v = __ldg(x + (size_t)j * ldx + r0 + r);
             else if (j == p0)
                 v = w ? __ldg(w + r0 + r) : 0.0;
             else
                 v = y ? __ldg(y + r0 + r) : 0.0;
         }
-        tile[r * tw + j] = v;
+        tile[j * tp + r] = v;
     }
-    __syncthreads();
-    const int p = nmain + nprod;
-    const int ldi = (int)ld;
-    for (int e = threadIdx.x; e < rows * ldi; e += blockDim.x) {
-        const int r = e / ldi, c = e % ldi;  // consecutive threads -> consecutive columns
-        const double *t = tile + r * tw;
-        double v;
+    const int p = nmain + nprod, ldi = (int)ld, ONE = p0 + 2, ZERO = p0 + 3;
+    for (int c = threadIdx.x; c < ldi; c += blockDim.x) {
+        short2 f;
         if (c < nmain)
-            v = t[c];
+            f = make_short2((short)c, (short)ONE);
         else if (c < p) {
             const int q = c - nmain;
-            v = t[q / p0] * t[q % p0];
+            f = make_short2((short)(q / p0), (short)(q % p0));
         } else if (c == p)
-            v = t[p0];
+            f = make_short2((short)p0, (short)ONE);
         else if (c == p + 1)
-            v = t[p0 + 1];
+            f = make_short2((short)(p0 + 1), (short)ONE);
         else if (c == p + 2)
-            v = 1.0;
+            f = make_short2((short)ONE, (short)ONE);
         else
-            v = 0.0;
-        X[(size_t)(r0 + r) * ld + c] = v;
+            f = make_short2((short)ZERO, (short)ZERO);
+        lut[c] = f;
+    }
+    __syncthreads();
+    const int half = ldi >> 1;  // ld is a multiple of 32
+    for (int e = threadIdx.x; e < rows * half; e += blockDim.x) {
+        const int r = e / half, c = 2 * (e - r * half);  // one division per 16-byte store
+        const short2 f0 = lut[c], f1 = lut[c + 1];
+        const double v0 = tile[f0.x * tp + r] * tile[f0.y * tp + r];
+        const double v1 = tile[f1.x * tp + r] * tile[f1.y * tp + r];
+        *reinterpret_cast<double2 *>(X + (size_t)(r0 + r) * ld + c) = make_double2(v0, v1);
     }
 }
 
@@ -219,16 +284,18 @@ int ate_i_standardize(ate_ctx *ctx, double *d_x, long long n, int p, const int *
     return 0;
 }
 
-int ate_i_build_design(ate_ctx *ctx, const double *d_xbase, long long n, int p0, int expand,
+int ate_i_build_design(ate_ctx *ctx, const double *d_xbase, long long ldx, long long n, int p0, int expand,
                        const double *d_w, const double *d_y, double *d_X, long long ld) {
     const int nmain = (expand == 1) ? 0 : p0;
     const int nprod = (expand == 0) ? 0 : p0 * p0;
-    if (nmain + nprod + 3 > ld) return ate_fail(ctx, -1, "build_design: ld too small");
-    const size_t smem = sizeof(double) * (size_t)(p0 + 2) * DES_ROWS;
+    if (nmain + nprod + 3 > ld || (ld & 31) != 0) return ate_fail(ctx, -1, "build_design: bad ld");
+    if (p0 + 4 > 32000) return ate_fail(ctx, -1, "build_design: p0 too large");
+    const size_t smem = sizeof(double) * (size_t)(p0 + 4) * (DES_ROWS + 1) + sizeof(short2) * (size_t)ld;
+    if (smem > 200 * 1024) return ate_fail(ctx, -1, "build_design: p0 = %d too large", p0);
     if (smem > 48 * 1024)
         ATE_CUDA(ctx, cudaFuncSetAttribute(build_design_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long blocks = (n + DES_ROWS - 1) / DES_ROWS;
-    build_design_kernel<<<(unsigned)blocks, 256, smem, ctx->stream>>>(d_xbase, n, p0, nmain, nprod, d_w, d_y, d_X, ld);
+    build_design_kernel<<<(unsigned)blocks, 256, smem, ctx->stream>>>(d_xbase, ldx, n, p0, nmain, nprod, d_w, d_y, d_X, ld);
     ATE_LAUNCHED(ctx);
     return 0;
 }

@@ -24,7 +24,7 @@
 // Algorithmic work per launch: nrows * p * (p + 1) flop (lower triangle incl.
 // diagonal), nrows * (p + 1) * 8 bytes.
 #include "common.cuh"
-#include "irls_step.cuh"
+#include "common.cuh"
 
 namespace {
 
@@ -349,7 +349,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
             void *scr_l = nullptr;
             ATE_TRY(ate_gram_scratch(ctx, sizeof(double) * 1024 * (size_t)nblk_l * nch, &scr_l));
             cudaEvent_t e0 = nullptr, e1 = nullptr;
-            if (ctx->profile) {
+            if (ctx->profile & 2) {
                 ATE_CUDA(ctx, cudaEventCreate(&e0));
                 ATE_CUDA(ctx, cudaEventCreate(&e1));
                 ATE_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
@@ -358,7 +358,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
                                                                             hole_len, rpc_l, v, nblk_l, st, nullptr,
                                                                             (double *)scr_l, wA, offB);
             ATE_LAUNCHED(ctx);
-            if (ctx->profile) {
+            if (ctx->profile & 2) {
                 ATE_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
                 ctx->prof_events.emplace_back(e0, e1);
                 ctx->prof_shape.emplace_back(-nc, nrows);
@@ -406,7 +406,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
     ATE_TRY(ate_gram_scratch(ctx, sizeof(double) * 1024 * (size_t)nblk * nchunks, &scr));
     ATE_TRY(gram_allow_big_smem(ctx));
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (ctx->profile) {
+    if (ctx->profile & 2) {
         ATE_CUDA(ctx, cudaEventCreate(&e0));
         ATE_CUDA(ctx, cudaEventCreate(&e1));
         ATE_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
@@ -414,7 +414,7 @@ int ate_i_gram(ate_ctx *ctx, const double *X, long long ld, int p, const int32_t
     gram_dmma_kernel<<<dim3(ngroups, nchunks), G_THREADS, smem, ctx->stream>>>(
         X, ld, ncols, rows, row_begin, nrows, hole_begin, hole_len, rpc, v, nblk, stages, colidx, (double *)scr, 0, 0);
     ATE_LAUNCHED(ctx);
-    if (ctx->profile) {
+    if (ctx->profile & 2) {
         ATE_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
         ctx->prof_events.emplace_back(e0, e1);
         ctx->prof_shape.emplace_back(-p, nrows);

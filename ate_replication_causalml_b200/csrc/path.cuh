@@ -17,11 +17,15 @@
 //   d_list : device row ids of the subset, grouped by inner fold (segment f = rows whose
 //            cv.glmnet foldid is f+1).  NULL = rows 0..nt-1 in order (only with nseg <= 1).
 //   seg    : nseg+1 offsets into d_list.  nseg == 0: plain glmnet() on the subset, no CV.
+// When several ranks share the fit (PathOpts::shard_count > 1) every rank holds a slice of the rows:
+// d_list / nt / seg describe THIS rank's rows; nt_global / seg_global (fold sizes) the whole problem.
 struct CvProblem {
     const int32_t *d_list = nullptr;
     long long nt = 0;
     int nseg = 0;
     std::vector<long long> seg;
+    long long nt_global = 0;              // 0: same as nt
+    std::vector<long long> seg_global;    // nseg fold sizes over all ranks; empty: same as seg
 };
 
 struct CvOut {
@@ -37,8 +41,14 @@ struct PathOpts {
     int nulam = 0;
     double thr = 1.0e-7;
     int maxit = 100000;
-    int shard_rank = 0, shard_count = 1;  // cv-fold paths dealt round-robin over ranks
+    int shard_rank = 0, shard_count = 1;  // ranks sharing the fit, each holding a slice of the rows
 };
+
+// Sum a device buffer of doubles over the ranks sharing the fit, in place, on the ctx stream: NCCL when
+// the ctx has a communicator (ate_ctx_nccl_init), else through the host hook (ate_ctx_set_allreduce).
+int ate_i_allreduce(ate_ctx *ctx, double *dbuf, long long count);
+// every rank contributes `chunk` doubles at dsend; drecv receives nranks * chunk doubles, rank-major
+int ate_i_allgather(ate_ctx *ctx, const double *dsend, double *drecv, long long chunk, int rank, int nranks);
 
 // X: row-major design, features are columns [0, ni); iy / i1: response and ones columns.
 int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int iy, int i1,
@@ -47,6 +57,7 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
 struct IrlsStats {
     int rounds = 0;
     double solves = 0.0, sum_strong = 0.0, sum_strong2 = 0.0;
+    double step_launches = 0.0, row_fits = 0.0, rows_staged = 0.0, list_misses = 0.0;
 };
 int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int iy,
                       const double *vp_host, const PathOpts &po, const std::vector<CvProblem> &probs,

@@ -10,39 +10,45 @@
 //   lognet_pre_kernel  : one CTA per fit: convergence test of the previous quadratic, KKT check,
 //                        recording / advancing lambda, strong-rule update.  Only the strong
 //                        set's columns enter the Gram (on average ~1/6 of p at C1, i.e. ~4 % of
-//                        the flops).  If a column joined that the fused step's list missed
-//                        (rare: the list carries a 10 % margin), a plain Gram over the exact
-//                        list runs before the solve.
+//                        the flops).  If a column joined that the step's list missed (rare: the
+//                        list carries a 10 % margin), the solve is put off by one round: the list
+//                        is rebuilt around the exact strong set and the step repeats at the same
+//                        coefficients -- no host decision is involved.
 //   lognet_solve_kernel: one CTA per fit.  Standardises the compact H in place (lstandard1's
 //                        centring and 1/N scaling are affine in H, X^T v, sum v), then follows
 //                        lognet2n's loop order exactly -- strong-set sweep, intercept step,
 //                        active-set loop -- with g_k = <r, x_k> kept current by covariance
 //                        updates g -= d * H[:,k].  In exact arithmetic the iterates equal glmnet's.
 // All fits of a batch (the full-data fits of every outer fold, then all their CV folds) advance
-// one IRLS step per round; finished fits drop out.  The host reads two small flag vectors per
-// round (after the bookkeeping: who is done / needs a Gram; after the solve: next list lengths).
+// one IRLS step per round, ONE launch of the step kernel for all of them (irls_round.cu); finished
+// fits drop out.  The host reads one small flag vector per round (who is done, next list lengths).
+// When several GPUs share the fit each holds a slice of the rows: the packed per-fit sums and Grams
+// of a round are all-reduced on the stream before the bookkeeping, after which every rank runs the
+// same p x p work on the same numbers and takes the same decisions.
 #include <math.h>
 #include <stdlib.h>
 
 #include <chrono>
 
-#include "irls_step.cuh"
+#include "irls_round.cuh"
 #include "path.cuh"
 
 namespace {
 
 enum { PH_INIT = 0, PH_REFRESH = 1 };
 enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_SUMS, SD_SUMS2, SD_SUMA, SD_N };
-enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_NG, SI_HMAP, SI_MISS, SI_N };
+enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_NG, SI_RETRY, SI_MISS, SI_N };
 // sums layout: gr[ni] = X^T r, hx[ni] = X^T v, hxx[ni] = sum v x^2, then XMZ, SR, DEV
 enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
 
 struct LognetFit {
     const double *X;      // the design this fit reads: the shared one (with a row list) or a
-    long long ld;         //   private contiguous copy of its rows (list == NULL)
+    long long ld;         //   private contiguous copy of its problem's rows (list == NULL)
     const int32_t *list;  // row ids (NULL = identity)
-    long long nt, hole_begin, hole_len;
-    int ni, iy, owned, ldh, ncs;  // ncs: columns staged per row by the fused step = its zero slot
+    long long hole_begin, hole_len;  // this rank's rows of the held-out inner fold (positions in the problem's rows)
+    double nt;            // observations of the fit over ALL ranks
+    int prob, seg;        // problem index; held-out segment (-1: the full-data fit)
+    int ni, iy, ldh, ncs;  // ncs: columns staged per row by the step kernel = its zero slot
     const double *vp;
     double flmin;
     const double *ulam;
@@ -50,9 +56,6 @@ struct LognetFit {
     int nlam;
     double thr;
     int maxit;
-    double *v;        // [nt] IRLS weights of the current step
-    double *H;        // ldh x ldh: X_S^T V X_S over the strong set, in order of entry
-    double *sums;     // 3 ni + SU_N
     double *coef;     // ni + 1 (a0 last): raw-scale coefficients for the next eval
     double *st_d;     // b, bs, xv, ga, xm, xs, vq [7 ni] + SD_N
     int *st_i;        // ixx, mm, mlist, ju, spos, gpos [6 ni] + slist [ldh] + glist [ldh] + SI_N
@@ -62,9 +65,12 @@ struct LognetFit {
 constexpr int EV_THREADS = 256;
 constexpr int CD_THREADS = 256;
 
-__device__ __forceinline__ long long phys_pos(const LognetFit &f, long long t) {
-    return t + (t >= f.hole_begin ? f.hole_len : 0);
-}
+// where a fit's sums and Gram of the current round sit (the packed buffer of irls_round.cu)
+struct RoundDev {
+    const double *sums;  // X^T r [ni], X^T v [ni], sum v x^2 [ni], then XMZ, SR, DEV
+    double *H;           // ldh x ldh over the column list of the round
+    int ldh, pad;
+};
 __device__ __forceinline__ int *fit_slist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni; }
 __device__ __forceinline__ int *fit_glist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + f.ldh; }
 __device__ __forceinline__ int *fit_scal_i(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + 2 * (size_t)f.ldh; }
@@ -82,23 +88,38 @@ fold_partials_kernel(const double *__restrict__ partials, int nparts, int len, d
     if (lane == 0) out[e] = s;
 }
 
-// sum of the response column over the fit's rows -> q0, bz; arms the first eval
+// sum of the response column over inner-fold segment blockIdx.y of problem blockIdx.x (this rank's rows)
+struct SegDesc {
+    const double *X;
+    long long ld;
+    const int32_t *list;
+    long long begin, end;
+    int iy, pad;
+};
 __global__ void __launch_bounds__(256)
-lognet_init_kernel(const LognetFit *__restrict__ fits) {
-    const LognetFit f = fits[blockIdx.x];
-    const double *X = f.X;
-    const long long ld = f.ld;
+lognet_ysum_kernel(const SegDesc *__restrict__ segs, double *__restrict__ out) {
+    const SegDesc sgm = segs[blockIdx.x];
     __shared__ double red[32];
     double acc[1] = {0.0};
-    for (long long t = threadIdx.x; t < f.nt; t += blockDim.x) {
-        const long long pp = phys_pos(f, t);
-        const long long row = f.list ? (long long)__ldg(f.list + pp) : pp;
-        acc[0] += __ldg(X + (size_t)row * (size_t)ld + f.iy);
+    for (long long t = sgm.begin + threadIdx.x; t < sgm.end; t += blockDim.x) {
+        const long long row = sgm.list ? (long long)__ldg(sgm.list + t) : t;
+        acc[0] += __ldg(sgm.X + (size_t)row * (size_t)sgm.ld + sgm.iy);
     }
     block_sum<1>(acc, red);
+    if (threadIdx.x == 0) out[blockIdx.x] = acc[0];
+}
+
+// q0 = mean of the response over the fit's rows (the problem's rows minus the held-out segment),
+// bz = logit(q0); arms the first evaluation pass.  ysum[prob * nsegp + s], nsegp = max(nseg, 1).
+__global__ void __launch_bounds__(256)
+lognet_init_kernel(const LognetFit *__restrict__ fits, const double *__restrict__ ysum, int nsegp) {
+    const LognetFit f = fits[blockIdx.x];
     for (int j = threadIdx.x; j < f.ni; j += blockDim.x) f.coef[j] = 0.0;
     if (threadIdx.x == 0) {
-        const double q0 = acc[0] / (double)f.nt;
+        double tot = 0.0;
+        for (int sg = 0; sg < nsegp; ++sg)
+            if (sg != f.seg) tot += ysum[f.prob * nsegp + sg];
+        const double q0 = tot / f.nt;
         const double bz = log(q0 / (1.0 - q0));
         f.coef[f.ni] = bz;
         double *sd = fit_scal_d(f);
@@ -109,7 +130,6 @@ lognet_init_kernel(const LognetFit *__restrict__ fits) {
         sd[SD_BZ] = bz;
         sd[SD_B0] = bz;
         si[SI_PHASE] = PH_INIT;
-        if (!f.owned) si[SI_DONE] = 1;  // another rank solves this cv-fold path
         if (q0 <= GLM_PMIN) {
             si[SI_JERR] = 8001;
             si[SI_DONE] = 1;
@@ -146,24 +166,23 @@ __device__ __forceinline__ double bmax_all(double v, double *red) {
 
 // ---- IRLS round, part 1: bookkeeping that needs only the evaluation pass --------------------
 // Convergence of the previous quadratic, KKT re-check, recording lambda, advancing it, and the
-// strong-set update.  Leaves the (padded) strong-column list for the Gram pass and tells the host
-// how many columns it holds.  flags_out[4*fit + {0,1,2,3}] = {done, nS, solve pending, Gram missing}:
-// the fused step computed H over last round's prediction of the strong set; when a column joined
-// that the prediction missed, the host runs a plain Gram over the exact list before the solve.
+// strong-set update.  The step computed H over last round's prediction of the strong set; when a
+// column joined that the prediction missed, SI_RETRY is raised: the solve kernel then only rebuilds
+// the list (around the exact strong set), the step repeats at the same coefficients, and the next
+// visit here goes straight to the solve.
 __global__ void __launch_bounds__(CD_THREADS)
-lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_out) {
+lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev) {
     const LognetFit f = fits[blockIdx.x];
+    const RoundDev rd = rdev[blockIdx.x];
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
     if (si[SI_DONE]) {
-        if (tid == 0) {
-            flags_out[4 * blockIdx.x] = 1;
-            flags_out[4 * blockIdx.x + 1] = 0;
-            flags_out[4 * blockIdx.x + 2] = 0;
-            flags_out[4 * blockIdx.x + 3] = 0;
-            si[SI_SOLVE] = 0;
-        }
+        if (tid == 0) si[SI_SOLVE] = 0;
+        return;
+    }
+    if (si[SI_RETRY]) {  // the bookkeeping of this step was done last round; H now covers the strong set
+        if (tid == 0) si[SI_RETRY] = 0;
         return;
     }
     extern __shared__ double sm[];
@@ -172,9 +191,9 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
            *Gxs = Gxm + ni, *Gvq = Gxs + ni;
     int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni, *Ggpos = Gspos + ni;
     int *slist = fit_slist(f);
-    const double *gr = f.sums, *hx = f.sums + ni, *hxx = f.sums + 2 * ni;
-    const double xmz = f.sums[3 * ni + SU_XMZ], sr_in = f.sums[3 * ni + SU_SR];
-    const double devsum = f.sums[3 * ni + SU_DEV];
+    const double *gr = rd.sums, *hx = rd.sums + ni, *hxx = rd.sums + 2 * ni;
+    const double xmz = rd.sums[3 * ni + SU_XMZ], sr_in = rd.sums[3 * ni + SU_SR];
+    const double devsum = rd.sums[3 * ni + SU_DEV];
     const double pmin = GLM_PMIN, vmin = (1.0 + pmin) * pmin * (1.0 - pmin);
 
     int ilm = si[SI_ILM], nS = si[SI_NS];
@@ -323,9 +342,10 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
                 Gixx[k] = 1;
                 Gspos[k] = nS;
                 slist[nS++] = k;
-                if (Ggpos[k] < 0) miss = 1;  // not in the list the fused step built H over
+                if (Ggpos[k] < 0) miss = 1;  // not in the list the step built H over
             }
-        si[SI_HMAP] = miss;                   // 1: the host recomputes H over slist -> positions = spos
+        if (finished) miss = 0;
+        si[SI_RETRY] = miss;  // 1: the step repeats over a list rebuilt around the strong set
         si[SI_MISS] += miss;
         sd[SD_AL] = al;
         sd[SD_AL0] = al0;
@@ -343,43 +363,45 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, int *__restrict__ flags_ou
             // sequence is handed to the CV folds
             if (f.flmin < 1.0 && si[SI_LMU] > 2) f.alm[0] = exp(2.0 * log(f.alm[1]) - log(f.alm[2]));
         }
-        flags_out[4 * blockIdx.x] = finished ? 1 : 0;
-        flags_out[4 * blockIdx.x + 1] = nS;
-        flags_out[4 * blockIdx.x + 2] = finished ? 0 : 1;
-        flags_out[4 * blockIdx.x + 3] = (!finished && miss && nS > 0) ? 1 : 0;
     }
 }
 
 // ---- IRLS round, part 2: solve the penalised quadratic on the strong set -------------------
-// H holds X_L^T V X_L over a column list L: the list the fused step used (positions gpos) or, after
-// a missed prediction, the exact strong list (positions spos).  At the end the list for the next
-// fused step is rebuilt: the strong set plus every column whose gradient is within 10 % of the
-// next strong-rule / KKT threshold.  ng_out[fit] = its length.
+// H holds X_L^T V X_L over the column list L the step used (positions gpos).  At the end the list for
+// the next step is rebuilt: the strong set plus every column whose gradient is within 10 % of the
+// next strong-rule / KKT threshold, ordered so that the MMA warps' gathered operand loads spread over
+// the shared-memory banks.  flags_out[2 fit + {0, 1}] = {done, length of the next list}.
 __global__ void __launch_bounds__(CD_THREADS)
-lognet_solve_kernel(const LognetFit *__restrict__ fits, int *__restrict__ ng_out) {
+lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev, int *__restrict__ flags_out) {
     const LognetFit f = fits[blockIdx.x];
-    const int ni = f.ni, tid = threadIdx.x, T = blockDim.x, ldh = f.ldh;
+    const RoundDev rd = rdev[blockIdx.x];
+    const int ni = f.ni, tid = threadIdx.x, T = blockDim.x, ldh = rd.ldh;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
     if (si[SI_DONE] || !si[SI_SOLVE]) {
-        if (tid == 0) ng_out[blockIdx.x] = si[SI_DONE] ? 0 : si[SI_NG];
+        if (tid == 0) {
+            flags_out[2 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
+            flags_out[2 * blockIdx.x + 1] = si[SI_DONE] ? 0 : si[SI_NG];
+        }
         return;
     }
+    const bool retry = si[SI_RETRY] != 0;  // list rebuild only: H does not cover the strong set yet
     extern __shared__ double sm[];
     double *b = sm, *g = b + ni, *hxs = g + ni, *xv = hxs + ni, *vq = xv + ni, *red = vq + ni;  // red[32]
     int *ixx = reinterpret_cast<int *>(red + 32), *mm = ixx + ni, *ml = mm + ni, *hp = ml + ni,
-        *sl = hp + ni;
+        *sl = hp + ni, *cand = sl + f.ldh, *srt = cand + f.ldh;
     double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gxm = Gxv + 2 * ni, *Gxs = Gxm + ni,
            *Gvq = Gxs + ni;
     int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni,
         *Ggpos = Gspos + ni;
     const int *slist = fit_slist(f);
     int *glist = fit_glist(f);
-    double *H = f.H;
-    const double *gr = f.sums, *hx = f.sums + ni;
-    const double xmz = f.sums[3 * ni + SU_XMZ], sr_in = f.sums[3 * ni + SU_SR];
+    double *H = rd.H;
+    const double *gr = rd.sums, *hx = rd.sums + ni;
+    const double xmz = rd.sums[3 * ni + SU_XMZ], sr_in = rd.sums[3 * ni + SU_SR];
     const int nS = si[SI_NS], ilm = si[SI_ILM];
-    const int *hmap = si[SI_HMAP] ? Gspos : Ggpos;
+    const int *hmap = Ggpos;
+    (void)Gspos;
     int nin = si[SI_NIN], nlp = si[SI_NLP];
     double b0 = sd[SD_B0];
     const double al1 = sd[SD_AL], shr = sd[SD_SHR];
@@ -396,10 +418,12 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, int *__restrict__ ng_out
         g[j] = ok ? (gr[j] - m * sr_in) / s : 0.0;
         hxs[j] = ok ? (hx[j] - m * xmz) / s : 0.0;
         xv[j] = 0.0;
-        Gbs[j] = b[j];
+        if (!retry) Gbs[j] = b[j];
     }
     for (int c = tid; c < nS; c += T) sl[c] = slist[c];
     __syncthreads();
+    bool fail = false;
+    if (!retry) {
     // standardise the strong block of H in place: lstandard1's centring and scaling are affine in it
     for (int e = tid; e < nS * nS; e += T) {
         const int a = e / nS, c = e - a * nS;
@@ -421,7 +445,6 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, int *__restrict__ ng_out
     }
     __syncthreads();
     double sr = sr_in;
-    bool fail = false;
     for (;;) {
         ++nlp;
         double dlx = 0.0;
@@ -505,16 +528,18 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, int *__restrict__ ng_out
         }
         if (fail) break;
     }
+    }  // !retry
     // ---- coefficients for the next evaluation pass, on the raw x scale ----
     double part = 0.0;
-    for (int j = tid; j < ni; j += T) {
-        const double bj = (b[j] != 0.0) ? b[j] / Gxs[j] : 0.0;
-        f.coef[j] = bj;
-        part += bj * Gxm[j];
-        Gb[j] = b[j];
-        Gmm[j] = mm[j];
-        Gml[j] = ml[j];
-    }
+    if (!retry)
+        for (int j = tid; j < ni; j += T) {
+            const double bj = (b[j] != 0.0) ? b[j] / Gxs[j] : 0.0;
+            f.coef[j] = bj;
+            part += bj * Gxm[j];
+            Gb[j] = b[j];
+            Gmm[j] = mm[j];
+            Gml[j] = ml[j];
+        }
     const double dotbm = bsum_all(part, red);
     // ---- column list of the next fused step: the strong set, then the likely joiners.  g[] of a
     //      non-strong column is still the gradient this round started from. ----
@@ -540,28 +565,46 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, int *__restrict__ ng_out
     __syncthreads();
     if (tid == 0) {
         int nG = 0;
-        for (int c = 0; c < nS; ++c) {
-            glist[nG] = sl[c];
-            Ggpos[sl[c]] = nG++;
-        }
-        for (int k = 0; k < ni && nG < ldh; ++k)
-            if (!ixx[k] && Gju[k] && fabs(g[k]) > tnext * vq[k]) {
-                glist[nG] = k;
-                Ggpos[k] = nG++;
+        for (int c = 0; c < nS; ++c) cand[nG++] = sl[c];
+        for (int k = 0; k < ni && nG < f.ldh; ++k)
+            if (!ixx[k] && Gju[k] && fabs(g[k]) > tnext * vq[k]) cand[nG++] = k;
+        // Order of the list.  An MMA warp loads, per 8x8 tile, 8 list columns x 4 staged rows; the rows
+        // sit 4 (mod 8) doubles apart, so the 8 columns spread evenly over the 16 eight-byte banks exactly
+        // when every residue class mod 4 holds two of them.  Deal the columns into groups of eight that
+        // way while all four classes last; the remainder follows in any order.
+        int cnt4[4] = {0, 0, 0, 0}, beg4[4], pos4[4];
+        for (int c = 0; c < nG; ++c) cnt4[cand[c] & 3]++;
+        beg4[0] = 0;
+        for (int q = 1; q < 4; ++q) beg4[q] = beg4[q - 1] + cnt4[q - 1];
+        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
+        for (int c = 0; c < nG; ++c) srt[pos4[cand[c] & 3]++] = cand[c];
+        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
+        int out = 0;
+        while (cnt4[0] >= 2 && cnt4[1] >= 2 && cnt4[2] >= 2 && cnt4[3] >= 2)
+            for (int q = 0; q < 4; ++q) {
+                glist[out++] = srt[pos4[q]++];
+                glist[out++] = srt[pos4[q]++];
+                cnt4[q] -= 2;
             }
+        for (int q = 0; q < 4; ++q)
+            while (cnt4[q]-- > 0) glist[out++] = srt[pos4[q]++];
+        for (int c = 0; c < nG; ++c) Ggpos[glist[c]] = c;
         const int npad = (nG + 31) / 32 * 32;
-        for (int c = nG; c < npad && c < ldh; ++c) glist[c] = f.ncs;
+        for (int c = nG; c < npad && c < f.ldh; ++c) glist[c] = f.ncs;
         si[SI_NG] = nG;
-        ng_out[blockIdx.x] = nG;
-        f.coef[ni] = b0 - dotbm;
-        sd[SD_B0] = b0;
-        si[SI_NIN] = nin;
-        si[SI_NLP] = nlp;
-        si[SI_ROUNDS] += 1;
-        if (fail) {
-            si[SI_JERR] = -(ilm + 1);
-            si[SI_DONE] = 1;
+        flags_out[2 * blockIdx.x + 1] = nG;
+        if (!retry) {
+            f.coef[ni] = b0 - dotbm;
+            sd[SD_B0] = b0;
+            si[SI_NIN] = nin;
+            si[SI_NLP] = nlp;
+            si[SI_ROUNDS] += 1;
+            if (fail) {
+                si[SI_JERR] = -(ilm + 1);
+                si[SI_DONE] = 1;
+            }
         }
+        flags_out[2 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
     }
 }
 
@@ -705,6 +748,19 @@ int ate_i_predict_rows(ate_ctx *ctx, const double *X, long long ld, int ni, cons
     return 0;
 }
 
+// bump allocator over one cached device block: the per-call state of the driver costs no cudaMalloc
+struct Carver {
+    char *base = nullptr;
+    size_t off = 0;
+    template <typename T>
+    T *take(size_t count) {
+        off = (off + 255) / 256 * 256;
+        T *p = base ? reinterpret_cast<T *>(base + off) : nullptr;
+        off += sizeof(T) * (count ? count : 1);
+        return p;
+    }
+};
+
 int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int iy,
                       const double *vp_host, const PathOpts &po, const std::vector<CvProblem> &probs,
                       std::vector<CvOut> &outs, IrlsStats *stats) {
@@ -716,68 +772,59 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     const int F = probs[0].nseg;
     for (auto &pr : probs)
         if (pr.nseg != F) return ate_fail(ctx, -1, "cv_binomial: problems must share nfolds");
+    const bool sharded = po.shard_count > 1;
     const int nlead = P, nfol = P * F, nfits = nlead + nfol;
-    // ---- buffers ----
-    size_t vr_total = 0;
-    std::vector<size_t> vr_off(nfits);
-    std::vector<long long> fit_nt(nfits), fit_hb(nfits), fit_hl(nfits);
-    for (int p = 0; p < P; ++p) {
-        fit_nt[p] = probs[p].nt; fit_hb[p] = probs[p].nt; fit_hl[p] = 0;
-        for (int f = 0; f < F; ++f) {
-            const int id = nlead + p * F + f;
-            fit_hb[id] = probs[p].seg[f];
-            fit_hl[id] = probs[p].seg[f + 1] - probs[p].seg[f];
-            fit_nt[id] = probs[p].nt - fit_hl[id];
-        }
-    }
-    for (int id = 0; id < nfits; ++id) {
-        vr_off[id] = vr_total;
-        vr_total += (size_t)fit_nt[id];
-    }
+    const int nsegp = F > 0 ? F : 1;
     const int plen = 3 * ni + SU_N;
     const int ldh = (ni + 31) / 32 * 32;
-    // the fused step stages [0, ncs) of every row: the features and the response column
+    // the step kernel stages [0, ncs) of every row: the features and the response column
     const int ncs = ((ni > iy ? ni : iy) + 1 + 7) / 8 * 8;
     if (ldh > ld || ncs > ld) return ate_fail(ctx, -1, "cv_binomial: design ld (%lld) too small for %d features", ld, ni);
-    const size_t h2 = (size_t)ldh * ldh;
     const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 6 * (size_t)ni + 2 * (size_t)ldh + SI_N;
     const size_t si_scal = 6 * (size_t)ni + 2 * (size_t)ldh;
     const size_t out_len = 3 * (size_t)nlam + (size_t)ni * nlam;
-    double *dvr_p = nullptr;
-    DevBuf<double> dH, dsums, dcoef, dstd, dout, dvp, dulam, dpart;
-    DevBuf<int> dsti, ddone, dnl;
-    DevBuf<LognetFit> dfits;
-    {
-        void *pool = nullptr;
-        ATE_TRY(ate_cached(ctx, "binom.v", vr_total * sizeof(double), &pool));
-        dvr_p = (double *)pool;
-    }
-    ATE_CUDA(ctx, dH.alloc(h2 * nfits));
-    ATE_CUDA(ctx, dsums.alloc((size_t)plen * nfits));
-    ATE_CUDA(ctx, dcoef.alloc((size_t)(ni + 1) * nfits));
-    ATE_CUDA(ctx, dstd.alloc(sd_len * nfits));
-    ATE_CUDA(ctx, dsti.alloc(si_len * nfits));
-    ATE_CUDA(ctx, dout.alloc(out_len * nfits));
-    ATE_CUDA(ctx, ddone.alloc(5 * (size_t)nfits));
-    ATE_CUDA(ctx, dfits.alloc(nfits));
-    ATE_CUDA(ctx, cudaMemsetAsync(dout.p, 0, sizeof(double) * out_len * nfits, ctx->stream));
-    ATE_CUDA(ctx, cudaMemsetAsync(ddone.p, 0, sizeof(int) * 5 * nfits, ctx->stream));
     const int ev_blocks = ctx->num_sms * 2;
-    ATE_CUDA(ctx, dpart.alloc((size_t)ev_blocks * (plen > nlam ? plen : nlam)));
-    if (vp_host) {
-        ATE_CUDA(ctx, dvp.alloc(ni));
-        ATE_CUDA(ctx, cudaMemcpyAsync(dvp.p, vp_host, sizeof(double) * ni, cudaMemcpyHostToDevice, ctx->stream));
+
+    // ---- device state: one cached block, carved ----
+    Carver cv;
+    double *dcoef, *dstd, *dout, *dvp, *dulam, *dysum, *dpart, *dcv;
+    int *dsti, *dflags, *dnl;
+    LognetFit *dfits;
+    RoundDev *drdev;
+    SegDesc *dsegs;
+    for (int pass = 0; pass < 2; ++pass) {
+        cv.off = 0;
+        dcoef = cv.take<double>((size_t)(ni + 1) * nfits);
+        dstd = cv.take<double>(sd_len * nfits);
+        dout = cv.take<double>(out_len * nfits);
+        dvp = cv.take<double>(ni);
+        dulam = cv.take<double>(nlam);
+        dysum = cv.take<double>((size_t)P * nsegp);
+        dpart = cv.take<double>((size_t)ev_blocks * nlam);
+        dcv = cv.take<double>((size_t)(nfol > 0 ? nfol : 1) * nlam);
+        dsti = cv.take<int>(si_len * nfits);
+        dflags = cv.take<int>(2 * (size_t)nfits);
+        dnl = cv.take<int>(1);
+        dfits = cv.take<LognetFit>(nfits);
+        drdev = cv.take<RoundDev>(nfits);
+        dsegs = cv.take<SegDesc>((size_t)P * nsegp);
+        if (pass == 0) {
+            void *blk = nullptr;
+            ATE_TRY(ate_cached(ctx, "binom.state", cv.off + 256, &blk));
+            cv.base = (char *)blk;
+        }
     }
+    ATE_CUDA(ctx, cudaMemsetAsync(dout, 0, sizeof(double) * out_len * nfits, ctx->stream));
+    ATE_CUDA(ctx, cudaMemsetAsync(dflags, 0, sizeof(int) * 2 * nfits, ctx->stream));
+    if (vp_host) ATE_CUDA(ctx, cudaMemcpyAsync(dvp, vp_host, sizeof(double) * ni, cudaMemcpyHostToDevice, ctx->stream));
     if (po.flmin >= 1.0) {
-        ATE_CUDA(ctx, dulam.alloc(nlam));
-        ATE_CUDA(ctx, cudaMemcpyAsync(dulam.p, po.ulam, sizeof(double) * nlam, cudaMemcpyHostToDevice, ctx->stream));
-        ATE_CUDA(ctx, dnl.alloc(1));
-        ATE_CUDA(ctx, cudaMemcpyAsync(dnl.p, &nlam, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        ATE_CUDA(ctx, cudaMemcpyAsync(dulam, po.ulam, sizeof(double) * nlam, cudaMemcpyHostToDevice, ctx->stream));
+        ATE_CUDA(ctx, cudaMemcpyAsync(dnl, &nlam, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     }
-    // Private contiguous copy of every problem's rows (in list order, pitch = staged width + 4):
-    // the fused step then stages a whole slot with one bulk copy instead of one per row, which
-    // is what lets it reach HBM speed.  ~100 passes per fit amortise the one gather.  Falls back
-    // to the shared design + row lists when the copies would not fit comfortably.
+    // Private contiguous copy of every problem's rows (in list order, pitch = staged width + 4): the
+    // step kernel then stages a whole slot with one bulk copy instead of one per row, which is what
+    // lets it reach HBM speed; ~100 passes per fit amortise the one gather.  Falls back to the shared
+    // design + row lists when the copies would not fit comfortably.
     const long long ldp = ncs + 4;
     std::vector<double *> Xp(P, nullptr);
     {
@@ -798,42 +845,71 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             }
         }
     }
+    std::vector<RoundProblem> rprobs(P);
+    for (int p = 0; p < P; ++p) {
+        rprobs[p].X = Xp[p] ? Xp[p] : X;
+        rprobs[p].ld = Xp[p] ? ldp : ld;
+        rprobs[p].rows = Xp[p] ? nullptr : probs[p].d_list;
+        rprobs[p].nrows = probs[p].nt;
+    }
+    // fit ids: [0, nlead) the full-data fits, then problem-major the cv-fold fits
     std::vector<LognetFit> hf(nfits);
+    std::vector<double> fit_nt(nfits), fit_hl_glob(nfits, 0.0);
     for (int id = 0; id < nfits; ++id) {
         const int p = id < nlead ? id : (id - nlead) / F;
+        const int sg = id < nlead ? -1 : (id - nlead) % F;
+        const CvProblem &pr = probs[p];
+        const double ntg = (double)(pr.nt_global > 0 ? pr.nt_global : pr.nt);
         LognetFit &g = hf[id];
-        g.X = Xp[p] ? Xp[p] : X;
-        g.ld = Xp[p] ? ldp : ld;
-        g.list = Xp[p] ? nullptr : probs[p].d_list;
-        g.nt = fit_nt[id]; g.hole_begin = fit_hb[id]; g.hole_len = fit_hl[id];
+        g.X = rprobs[p].X;
+        g.ld = rprobs[p].ld;
+        g.list = rprobs[p].rows;
+        g.hole_begin = sg < 0 ? 0 : pr.seg[sg];
+        g.hole_len = sg < 0 ? 0 : pr.seg[sg + 1] - pr.seg[sg];
+        if (sg >= 0) fit_hl_glob[id] = (double)(pr.seg_global.empty() ? g.hole_len : pr.seg_global[sg]);
+        g.nt = ntg - fit_hl_glob[id];
+        fit_nt[id] = g.nt;
+        g.prob = p; g.seg = sg;
         g.ni = ni; g.iy = iy; g.ldh = ldh; g.ncs = ncs;
-        // ranks sharing a fit deal BOTH the full-data fits and the cv-fold paths round-robin; the
-        // full-data results are exchanged between the two phases (below)
-        g.owned = (po.shard_count <= 1 || ((id < nlead ? id : id - nlead) % po.shard_count) == po.shard_rank) ? 1 : 0;
-        g.vp = vp_host ? dvp.p : nullptr;
+        g.vp = vp_host ? dvp : nullptr;
         g.nlam = nlam; g.thr = po.thr; g.maxit = po.maxit;
-        g.v = dvr_p + vr_off[id];
-        g.H = dH.p + h2 * id;
-        g.sums = dsums.p + (size_t)plen * id;
-        g.coef = dcoef.p + (size_t)(ni + 1) * id;
-        g.st_d = dstd.p + sd_len * id;
-        g.st_i = dsti.p + si_len * id;
-        double *o = dout.p + out_len * id;
+        g.coef = dcoef + (size_t)(ni + 1) * id;
+        g.st_d = dstd + sd_len * id;
+        g.st_i = dsti + si_len * id;
+        double *o = dout + out_len * id;
         g.alm = o; g.a0 = o + nlam; g.dev = o + 2 * nlam; g.beta = o + 3 * nlam;
         if (id < nlead) {
             g.flmin = po.flmin;
-            g.ulam = po.flmin >= 1.0 ? dulam.p : nullptr;
-            g.nlam_ptr = po.flmin >= 1.0 ? dnl.p : nullptr;
+            g.ulam = po.flmin >= 1.0 ? dulam : nullptr;
+            g.nlam_ptr = po.flmin >= 1.0 ? dnl : nullptr;
         } else {
             g.flmin = 1.0;
             g.ulam = hf[p].alm;
             g.nlam_ptr = hf[p].st_i + si_scal + SI_LMU;
         }
+        if (g.nt < 2.0) return ate_fail(ctx, -1, "cv_binomial: a fit with %g observations", g.nt);
     }
-    ATE_CUDA(ctx, cudaMemcpyAsync(dfits.p, hf.data(), sizeof(LognetFit) * nfits, cudaMemcpyHostToDevice, ctx->stream));
+    ATE_CUDA(ctx, cudaMemcpyAsync(dfits, hf.data(), sizeof(LognetFit) * nfits, cudaMemcpyHostToDevice, ctx->stream));
+    {
+        std::vector<SegDesc> hs((size_t)P * nsegp);
+        for (int p = 0; p < P; ++p)
+            for (int sg = 0; sg < nsegp; ++sg) {
+                SegDesc &d = hs[(size_t)p * nsegp + sg];
+                d.X = rprobs[p].X; d.ld = rprobs[p].ld; d.list = rprobs[p].rows; d.iy = iy; d.pad = 0;
+                d.begin = F > 0 ? probs[p].seg[sg] : 0;
+                d.end = F > 0 ? probs[p].seg[sg + 1] : probs[p].nt;
+            }
+        ATE_CUDA(ctx, cudaMemcpyAsync(dsegs, hs.data(), sizeof(SegDesc) * hs.size(), cudaMemcpyHostToDevice, ctx->stream));
+        lognet_ysum_kernel<<<P * nsegp, 256, 0, ctx->stream>>>(dsegs, dysum);
+        ATE_LAUNCHED(ctx);
+        if (sharded) ATE_TRY(ate_i_allreduce(ctx, dysum, (long long)P * nsegp));
+        ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // hs is a host temporary
+    }
+    lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits, dysum, nsegp);
+    ATE_LAUNCHED(ctx);
 
     const size_t pre_smem = sizeof(double) * ((size_t)ni + 32);
-    const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * (4 * (size_t)ni + ldh);
+    const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * (4 * (size_t)ni + 3 * (size_t)ldh);
     if (cd_smem > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
     if (cd_smem > 48 * 1024)
         ATE_CUDA(ctx, cudaFuncSetAttribute(lognet_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cd_smem));
@@ -841,117 +917,79 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
 
     const bool timing = getenv("ATE_TIMING") != nullptr;
     auto tnow = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-    double t_mark = 0.0, t_step = 0.0, t_pre = 0.0, t_gram = 0.0, t_solve = 0.0;
-    if (timing) { cudaStreamSynchronize(ctx->stream); t_mark = tnow(); }
-    lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits.p);
-    ATE_LAUNCHED(ctx);
-    if (timing) { cudaStreamSynchronize(ctx->stream); fprintf(stderr, "[ate timing] init %.1f ms\n", tnow() - t_mark); }
+    double t_host = 0.0, t_wait = 0.0, t_mark = tnow();
 
-    std::vector<int> hdone(nfits, 0), hflags(4 * (size_t)nfits, 0), hng(nfits, 0);
-    std::vector<char> started(nfits, 0);
-    for (int id = 0; id < nfits; ++id)
-        if (!hf[id].owned) hdone[id] = 1;
-    int *dflags = ddone.p, *dng = ddone.p + 4 * (size_t)nfits;
+    std::vector<int> hdone(nfits, 0), hng(nfits, 0);
+    void *hflags_v = nullptr, *hrdev_v = nullptr;
+    ATE_TRY(ate_cached_pinned(ctx, "binom.hflags", sizeof(int) * 2 * (size_t)nfits, &hflags_v));
+    ATE_TRY(ate_cached_pinned(ctx, "binom.hrdev", sizeof(RoundDev) * (size_t)nfits, &hrdev_v));
+    int *hflags = (int *)hflags_v;
+    RoundDev *hrdev = (RoundDev *)hrdev_v;
+    std::vector<RoundFit> rfits(nfits);
+    std::vector<RoundSlot> slots;
     int rounds = 0;
     const int max_rounds = nlam * 60 + 100;
-    // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds.
-    // One round = fused IRLS step (evaluation + Gram over the predicted list) -> bookkeeping ->
-    // (rarely) a Gram over the exact strong list -> coordinate-descent solve.
+    RoundStats rst;
+    // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds.  One
+    // round = step kernel for every live fit (evaluation + Gram over the predicted lists) -> (ranks
+    // sharing the fit: all-reduce of the packed results) -> bookkeeping -> coordinate-descent solve.
     for (int phase = 0; phase < 2; ++phase) {
         const int lo = phase == 0 ? 0 : nlead, hi = phase == 0 ? nlead : nfits;
         if (lo == hi) continue;
-        for (;;) {
+        for (int round_in_phase = 0;; ++round_in_phase) {
             int live = 0;
-            if (timing) { cudaStreamSynchronize(ctx->stream); t_mark = tnow(); }
-            for (int id = lo; id < hi; ++id) {
-                if (hdone[id]) continue;
+            for (int id = 0; id < nfits; ++id) {
+                RoundFit &r = rfits[id];
+                r.live = (id >= lo && id < hi && !hdone[id]) ? 1 : 0;
+                if (!r.live) continue;
                 ++live;
-                IrlsStep st;
-                st.X = hf[id].X; st.ld = hf[id].ld; st.ncols = ncs;
-                st.rows = hf[id].list; st.nrows = hf[id].nt;
-                st.hole_begin = hf[id].hole_begin; st.hole_len = hf[id].hole_len;
-                st.ni = ni; st.iy = iy; st.coef = hf[id].coef; st.w = 1.0 / (double)hf[id].nt;
-                st.colidx = hf[id].st_i + 6 * (size_t)ni + ldh;  // the list the last solve left
-                st.nG = hng[id];
-                st.H = hf[id].H; st.ldh = ldh; st.sums = hf[id].sums; st.v_out = hf[id].v;
-                st.init = started[id] ? 0 : 1;
-                started[id] = 1;
-                ATE_TRY(ate_i_irls_step(ctx, st));
+                r.prob = hf[id].prob;
+                r.hole_begin = hf[id].hole_begin;
+                r.hole_len = hf[id].hole_len;
+                r.w = 1.0 / fit_nt[id];
+                r.coef = hf[id].coef;
+                r.colidx = hf[id].st_i + 6 * (size_t)ni + ldh;  // the list the last solve left
+                r.nG = hng[id];
             }
             if (!live) break;
-            if (timing) { cudaStreamSynchronize(ctx->stream); const double t = tnow(); t_step += t - t_mark; t_mark = t; }
-            lognet_pre_kernel<<<hi - lo, CD_THREADS, pre_smem, ctx->stream>>>(dfits.p + lo, dflags + 4 * (size_t)lo);
+            double *packed = nullptr;
+            long long count = 0;
+            ATE_TRY(ate_i_irls_round(ctx, ncs, ni, iy, round_in_phase == 0 ? 1 : 0, rprobs, rfits, slots, &packed, &count, &rst));
+            for (int id = lo; id < hi; ++id) {
+                hrdev[id].sums = packed + slots[id].sums_off;
+                hrdev[id].H = packed + slots[id].H_off;
+                hrdev[id].ldh = slots[id].ldh;
+                hrdev[id].pad = 0;
+            }
+            ATE_CUDA(ctx, cudaMemcpyAsync(drdev + lo, hrdev + lo, sizeof(RoundDev) * (hi - lo), cudaMemcpyHostToDevice, ctx->stream));
+            if (sharded && count > 0) ATE_TRY(ate_i_allreduce(ctx, packed, count));
+            lognet_pre_kernel<<<hi - lo, CD_THREADS, pre_smem, ctx->stream>>>(dfits + lo, drdev + lo);
             ATE_LAUNCHED(ctx);
-            ATE_CUDA(ctx, cudaMemcpyAsync(hflags.data() + 4 * (size_t)lo, dflags + 4 * (size_t)lo,
-                                          sizeof(int) * 4 * (hi - lo), cudaMemcpyDeviceToHost, ctx->stream));
+            lognet_solve_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits + lo, drdev + lo, dflags + 2 * (size_t)lo);
+            ATE_LAUNCHED(ctx);
+            ATE_CUDA(ctx, cudaMemcpyAsync(hflags + 2 * (size_t)lo, dflags + 2 * (size_t)lo, sizeof(int) * 2 * (hi - lo),
+                                          cudaMemcpyDeviceToHost, ctx->stream));
+            if (timing) { const double t = tnow(); t_host += t - t_mark; t_mark = t; }
             ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-            if (timing) { const double t = tnow(); t_pre += t - t_mark; t_mark = t; }
-            int solving = 0;
+            if (timing) { const double t = tnow(); t_wait += t - t_mark; t_mark = t; }
             for (int id = lo; id < hi; ++id) {
                 if (hdone[id]) continue;
-                hdone[id] = hflags[4 * (size_t)id];
-                const int nS = hflags[4 * (size_t)id + 1];
-                if (!hflags[4 * (size_t)id + 2]) continue;
-                ++solving;
-                if (hflags[4 * (size_t)id + 3])  // a column joined that the fused step's list missed
-                    ATE_TRY(ate_i_gram(ctx, hf[id].X, hf[id].ld, nS, hf[id].list, 0, hf[id].nt, hf[id].v, hf[id].H,
-                                       hf[id].hole_begin, hf[id].hole_len, hf[id].st_i + 6 * (size_t)ni, ncs, ldh));
+                hdone[id] = hflags[2 * (size_t)id];
+                hng[id] = hflags[2 * (size_t)id + 1];
             }
-            if (timing) { cudaStreamSynchronize(ctx->stream); const double t = tnow(); t_gram += t - t_mark; t_mark = t; }
-            if (solving) {
-                lognet_solve_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits.p + lo, dng + lo);
-                ATE_LAUNCHED(ctx);
-                ATE_CUDA(ctx, cudaMemcpyAsync(hng.data() + lo, dng + lo, sizeof(int) * (hi - lo),
-                                              cudaMemcpyDeviceToHost, ctx->stream));
-                ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if (stats) {
+                stats->step_launches += 1;
+                stats->row_fits += (double)rst.row_fits;
+                stats->rows_staged += (double)rst.rows_staged;
             }
-            if (timing) { const double t = tnow(); t_solve += t - t_mark; t_mark = t; }
             if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
         }
-        if (phase == 0 && po.shard_count > 1 && nlead > 0) {
-            // Every full-data fit was solved by exactly one rank.  Its lambda sequence gates the
-            // cv-fold paths of ALL ranks and its path is the model that is returned, so each rank
-            // now receives the fits it did not solve: the records are zero-filled by non-owners and
-            // summed through the host all-reduce hook (x + 0 is exact: bit-identical to one GPU).
-            if (!ctx->allreduce) return ate_fail(ctx, -1, "cv_binomial: sharded fit but no all-reduce hook set");
-            const size_t rec = out_len + 4;  // path outputs, then lmu, nlp, jerr, dev0
-            std::vector<double> xb(rec * (size_t)nlead, 0.0), tmp(out_len);
-            std::vector<int> ti(SI_N);
-            for (int id = 0; id < nlead; ++id) {
-                if (!hf[id].owned) continue;
-                double *r = xb.data() + rec * (size_t)id;
-                ATE_CUDA(ctx, cudaMemcpyAsync(r, dout.p + out_len * id, sizeof(double) * out_len, cudaMemcpyDeviceToHost, ctx->stream));
-                ATE_CUDA(ctx, cudaMemcpyAsync(ti.data(), hf[id].st_i + si_scal, sizeof(int) * SI_N, cudaMemcpyDeviceToHost, ctx->stream));
-                ATE_CUDA(ctx, cudaMemcpyAsync(r + out_len + 3, hf[id].st_d + 7 * (size_t)ni + SD_DEV0, sizeof(double),
-                                              cudaMemcpyDeviceToHost, ctx->stream));
-                ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-                r[out_len] = ti[SI_LMU];
-                r[out_len + 1] = ti[SI_NLP];
-                r[out_len + 2] = ti[SI_JERR];
-            }
-            if (ctx->allreduce(ctx->allreduce_user, xb.data(), (long long)xb.size()) != 0)
-                return ate_fail(ctx, -4, "cv_binomial: all-reduce hook failed");
-            for (int id = 0; id < nlead; ++id) {
-                if (hf[id].owned) continue;
-                const double *r = xb.data() + rec * (size_t)id;
-                ATE_CUDA(ctx, cudaMemcpyAsync(dout.p + out_len * id, r, sizeof(double) * out_len, cudaMemcpyHostToDevice, ctx->stream));
-                const int iv3[3] = {(int)r[out_len], (int)r[out_len + 1], (int)r[out_len + 2]};
-                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_i + si_scal + SI_LMU, &iv3[0], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_i + si_scal + SI_NLP, &iv3[1], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_i + si_scal + SI_JERR, &iv3[2], sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-                ATE_CUDA(ctx, cudaMemcpyAsync(hf[id].st_d + 7 * (size_t)ni + SD_DEV0, r + out_len + 3, sizeof(double),
-                                              cudaMemcpyHostToDevice, ctx->stream));
-                ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // iv3 and xb are host temporaries
-            }
-        }
     }
+    if (timing)
+        fprintf(stderr, "[ate timing] cv_binomial: %d rounds, host %.1f ms (planning + launches), waiting on the GPU %.1f ms\n",
+                rounds, t_host, t_wait);
 
-    if (timing) {
-        fprintf(stderr, "[ate timing] rounds %d: fused steps %.1f ms, bookkeeping %.1f ms, fallback grams %.1f ms, solves %.1f ms\n",
-                rounds, t_step, t_pre, t_gram, t_solve);
-        t_mark = tnow();
-    }
-    // ---- held-out deviance of every CV fold at every lambda ----
+    // ---- held-out deviance of every CV fold at every lambda (this rank's rows of the fold) ----
     std::vector<double> hcv;
     if (F > 0) {
         int LC = (int)((96 * 1024) / (sizeof(double) * (size_t)ni));
@@ -965,62 +1003,40 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             return 0;
         });
         if (rc < 0) return ate_fail(ctx, -1, "cv_binomial: cannot size cv kernel");
-        DevBuf<double> dcv;
-        ATE_CUDA(ctx, dcv.alloc((size_t)nfol * nlam));
-        ATE_CUDA(ctx, cudaMemsetAsync(dcv.p, 0, sizeof(double) * (size_t)nfol * nlam, ctx->stream));
+        ATE_CUDA(ctx, cudaMemsetAsync(dcv, 0, sizeof(double) * (size_t)nfol * nlam, ctx->stream));
         for (int q = 0; q < nfol; ++q) {
             const int id = nlead + q;
-            if (!hf[id].owned) continue;
-            ATE_CUDA(ctx, cudaMemsetAsync(dpart.p, 0, sizeof(double) * (size_t)ev_blocks * nlam, ctx->stream));
+            ATE_CUDA(ctx, cudaMemsetAsync(dpart, 0, sizeof(double) * (size_t)ev_blocks * nlam, ctx->stream));
             dispatch_iter(ni, [&](auto it) {
                 constexpr int IT = decltype(it)::value;
-                lognet_cvdev_kernel<IT><<<dim3(ev_blocks, nchunk), 256, cv_smem, ctx->stream>>>(dfits.p, id, LC, dpart.p);
+                lognet_cvdev_kernel<IT><<<dim3(ev_blocks, nchunk), 256, cv_smem, ctx->stream>>>(dfits, id, LC, dpart);
                 return 0;
             });
             ATE_LAUNCHED(ctx);
-            fold_partials_kernel<<<(nlam + 7) / 8, 256, 0, ctx->stream>>>(dpart.p, ev_blocks, nlam, dcv.p + (size_t)q * nlam);
+            fold_partials_kernel<<<(nlam + 7) / 8, 256, 0, ctx->stream>>>(dpart, ev_blocks, nlam, dcv + (size_t)q * nlam);
             ATE_LAUNCHED(ctx);
         }
+        if (sharded) ATE_TRY(ate_i_allreduce(ctx, dcv, (long long)nfol * nlam));
         hcv.resize((size_t)nfol * nlam);
-        ATE_CUDA(ctx, cudaMemcpyAsync(hcv.data(), dcv.p, sizeof(double) * hcv.size(), cudaMemcpyDeviceToHost, ctx->stream));
+        ATE_CUDA(ctx, cudaMemcpyAsync(hcv.data(), dcv, sizeof(double) * hcv.size(), cudaMemcpyDeviceToHost, ctx->stream));
     }
-    if (timing) { cudaStreamSynchronize(ctx->stream); fprintf(stderr, "[ate timing] cv deviance %.1f ms\n", tnow() - t_mark); }
     std::vector<double> hout(out_len * (size_t)nlead), hsd(sd_len * (size_t)nfits);
     std::vector<int> hsi(si_len * (size_t)nfits);
-    ATE_CUDA(ctx, cudaMemcpyAsync(hout.data(), dout.p, sizeof(double) * hout.size(), cudaMemcpyDeviceToHost, ctx->stream));
-    ATE_CUDA(ctx, cudaMemcpyAsync(hsd.data(), dstd.p, sizeof(double) * hsd.size(), cudaMemcpyDeviceToHost, ctx->stream));
-    ATE_CUDA(ctx, cudaMemcpyAsync(hsi.data(), dsti.p, sizeof(int) * hsi.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    ATE_CUDA(ctx, cudaMemcpyAsync(hout.data(), dout, sizeof(double) * hout.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    ATE_CUDA(ctx, cudaMemcpyAsync(hsd.data(), dstd, sizeof(double) * hsd.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    ATE_CUDA(ctx, cudaMemcpyAsync(hsi.data(), dsti, sizeof(int) * hsi.size(), cudaMemcpyDeviceToHost, ctx->stream));
     ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 
     if (stats) {
         stats->rounds = rounds;
         for (int id = 0; id < nfits; ++id) {
-            if (!hf[id].owned) continue;
             const double *dv = hsd.data() + sd_len * (size_t)id + 7 * (size_t)ni;
             const int *iv = hsi.data() + si_len * (size_t)id + si_scal;
             stats->solves += iv[SI_ROUNDS];
             stats->sum_strong += dv[SD_SUMS];
             stats->sum_strong2 += dv[SD_SUMS2];
+            stats->list_misses += iv[SI_MISS];
         }
-    }
-    // ---- ranks sharing this fit: every cv-fold path was solved by exactly one of them ----
-    std::vector<double> fstat((size_t)nfol * 3, 0.0);  // lmu, nlp, jerr of each cv-fold path
-    for (int q = 0; q < nfol; ++q) {
-        const int id = nlead + q;
-        if (!hf[id].owned) continue;
-        const int *fv = hsi.data() + si_len * (size_t)id + si_scal;
-        fstat[3 * q] = fv[SI_LMU];
-        fstat[3 * q + 1] = fv[SI_NLP];
-        fstat[3 * q + 2] = fv[SI_JERR];
-    }
-    if (po.shard_count > 1 && F > 0) {
-        if (!ctx->allreduce) return ate_fail(ctx, -1, "cv_binomial: sharded fit but no all-reduce hook set");
-        for (int q = 0; q < nfol; ++q)
-            if (!hf[nlead + q].owned)
-                for (int l = 0; l < nlam; ++l) hcv[(size_t)q * nlam + l] = 0.0;
-        if (ctx->allreduce(ctx->allreduce_user, hcv.data(), (long long)hcv.size()) != 0 ||
-            ctx->allreduce(ctx->allreduce_user, fstat.data(), (long long)fstat.size()) != 0)
-            return ate_fail(ctx, -4, "cv_binomial: all-reduce hook failed");
     }
 
     outs.assign(P, CvOut());
@@ -1036,17 +1052,17 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         o.a0.assign(ob + nlam, ob + nlam + o.lmu);
         o.dev.assign(ob + 2 * nlam, ob + 2 * nlam + o.lmu);
         o.beta.assign(ob + 3 * nlam, ob + 3 * nlam + (size_t)ni * o.lmu);
-        o.nulldev = 2.0 * (double)probs[p].nt * dv[SD_DEV0];
+        o.nulldev = 2.0 * fit_nt[p] * dv[SD_DEV0];
         if (F > 0 && o.lmu > 0) {
             std::vector<double> cvk((size_t)F * o.lmu), wk(F);
             std::vector<int> nlk(F);
             for (int f = 0; f < F; ++f) {
                 const int id = nlead + p * F + f;
-                const double *fv = fstat.data() + 3 * (size_t)(p * F + f);
-                nlk[f] = (int)fv[0] < o.lmu ? (int)fv[0] : o.lmu;
-                if (fv[2] != 0 && o.jerr == 0) o.jerr = (int)fv[2];
-                o.nlp += (int)fv[1];
-                wk[f] = (double)fit_hl[id];
+                const int *fv = hsi.data() + si_len * (size_t)id + si_scal;
+                nlk[f] = fv[SI_LMU] < o.lmu ? fv[SI_LMU] : o.lmu;
+                if (fv[SI_JERR] != 0 && o.jerr == 0) o.jerr = fv[SI_JERR];
+                o.nlp += fv[SI_NLP];
+                wk[f] = fit_hl_glob[id];
                 for (int l = 0; l < o.lmu; ++l)
                     cvk[(size_t)f * o.lmu + l] = hcv[((size_t)p * F + f) * nlam + l] / wk[f];
             }

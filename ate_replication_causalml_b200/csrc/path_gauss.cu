@@ -419,6 +419,8 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
                 ATE_TRY(ate_i_gram(ctx, X, ld, mS, probs[p].d_list, probs[p].seg[f],
                                    probs[p].seg[f + 1] - probs[p].seg[f], nullptr,
                                    dSf.p + m2 * ((size_t)p * F + f)));
+        // ranks sharing the fit hold row slices: the moment matrices are additive over rows
+        if (po.shard_count > 1) ATE_TRY(ate_i_allreduce(ctx, dSf.p, (long long)(m2 * (size_t)nfol)));
         for (int p = 0; p < P; ++p) {
             sum_mats_kernel<<<ctx->num_sms, 256, 0, ctx->stream>>>(dSf.p + m2 * (size_t)p * F, F, m2, dStot.p + m2 * p);
             ATE_LAUNCHED(ctx);
@@ -426,6 +428,7 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     } else {
         for (int p = 0; p < P; ++p)
             ATE_TRY(ate_i_gram(ctx, X, ld, mS, probs[p].d_list, 0, probs[p].nt, nullptr, dStot.p + m2 * p));
+        if (po.shard_count > 1) ATE_TRY(ate_i_allreduce(ctx, dStot.p, (long long)(m2 * (size_t)P)));
     }
 
     // ---- per-fit workspace and outputs ----
@@ -538,7 +541,8 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
                 nlk[f] = fv[ni] < o.lmu ? fv[ni] : o.lmu;
                 if (fv[ni + 2] != 0 && o.jerr == 0) o.jerr = fv[ni + 2];
                 o.nlp += fv[ni + 1];
-                wk[f] = (double)(probs[p].seg[f + 1] - probs[p].seg[f]);
+                wk[f] = probs[p].seg_global.empty() ? (double)(probs[p].seg[f + 1] - probs[p].seg[f])
+                                                     : (double)probs[p].seg_global[f];
                 for (int l = 0; l < o.lmu; ++l) cvk[(size_t)f * o.lmu + l] = hcv[((size_t)p * F + f) * nlam + l];
             }
             ate_host_cv_summary(cvk, wk, nlk, F, o.lmu, o.lambda.data(), o.cvm, o.cvsd, &o.idx_min, &o.idx_1se);

@@ -20,11 +20,11 @@
 //     before any stream capture begins.
 #include <math.h>
 
-#include "common.cuh"
+#include "score_core.cuh"
 
 #define ATE_STATIC_SCORE_MAX_BLOCKS 1024
 #define ATE_STATIC_SCORE_MAX_N (1LL << 28)
-#define ATE_STATIC_SCORE_NV 6
+#define ATE_STATIC_SCORE_NV 6  /* = score_core::NV */
 // layout: [ticket: 16 B][result: 8 doubles][partials: MAX_BLOCKS x NV doubles]
 #define ATE_STATIC_SCORE_BYTES (16 + 64 + 8 * ATE_STATIC_SCORE_NV * ATE_STATIC_SCORE_MAX_BLOCKS)
 
@@ -37,57 +37,17 @@ constexpr int ST_THREADS = 256;
 constexpr int ST_MAX_DEVICES = 64;
 void *g_scratch_addr[ST_MAX_DEVICES] = {nullptr};  // device address of the array, per device
 
+// the same device code as aipw_score_kernel (score_core.cuh); only where the partials live differs
 __global__ void __launch_bounds__(ST_THREADS)
 aipw_score_static_kernel(long long n, const double *__restrict__ w, const double *__restrict__ y,
                          const double *__restrict__ p, const double *__restrict__ m0,
                          const double *__restrict__ m1, double *__restrict__ partials,
                          unsigned int *__restrict__ ticket, double *__restrict__ out) {
-    __shared__ double red[ATE_STATIC_SCORE_NV * 32];
+    __shared__ double red[score_core::NV * 32];
     __shared__ bool is_last;
-    double acc[ATE_STATIC_SCORE_NV] = {0, 0, 0, 0, 0, 0};
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const double wi = __ldg(w + i), yi = __ldg(y + i), pi = __ldg(p + i);
-        const double a0 = __ldg(m0 + i), a1 = __ldg(m1 + i);
-        // ate_functions.R:241-242 and the summand of :255, term by term as written there
-        const double e1 = wi * (yi - a1) / pi + (1.0 - wi) * (yi - a0) / (1.0 - pi);
-        const double e2 = a1 - a0;
-        const double J = (wi * yi) / pi - a1 * (wi - pi) / pi -
-                         (((1.0 - wi) * yi / (1.0 - pi)) + (a0 * (wi - pi) / (1.0 - pi)));
-        if (!isnan(e1)) {  // mean(est1, na.rm = TRUE)
-            acc[0] += e1;
-            acc[1] += 1.0;
-        }
-        acc[2] += e2;
-        acc[3] += J;
-        acc[4] += J * J;
-    }
-    block_sum<ATE_STATIC_SCORE_NV>(acc, red);
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int k = 0; k < ATE_STATIC_SCORE_NV; ++k)
-            partials[(size_t)blockIdx.x * ATE_STATIC_SCORE_NV + k] = acc[k];
-        __threadfence();
-        is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    if (threadIdx.x < ATE_STATIC_SCORE_NV) {  // fold the blocks in order: reproducible
-        double s = 0.0;
-        for (unsigned int b = 0; b < gridDim.x; ++b)
-            s += ((volatile double *)partials)[(size_t)b * ATE_STATIC_SCORE_NV + threadIdx.x];
-        red[threadIdx.x] = s;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const double dn = (double)n;
-        const double tau = red[0] / red[1] + red[2] / dn;
-        double ss = red[4] - 2.0 * tau * red[3] + dn * tau * tau;
-        if (ss < 0.0) ss = 0.0;
-        out[0] = tau;
-        out[1] = sqrt(ss) / dn;
-    }
+    double acc[score_core::NV] = {0, 0, 0, 0, 0, 0};
+    score_core::accumulate<false>(n, w, y, p, m0, m1, nullptr, nullptr, nullptr, acc);
+    score_core::finish(acc, red, &is_last, n, partials, ticket, out);
 }
 
 }  // namespace

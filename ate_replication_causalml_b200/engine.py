@@ -63,7 +63,8 @@ class Engine:
     def launches(self) -> int:
         return int(self._lib.ate_launch_count(self._h))
 
-    def profile_enable(self, on=True):
+    def profile_enable(self, on=1):
+        """0 off, 1 the IRLS step kernel, 2 the full-width Gram kernel, 3 both."""
         self._chk(self._lib.ate_profile_enable(self._h, int(on)), "ate_profile_enable")
 
     def profile_read(self):
@@ -156,6 +157,33 @@ class Engine:
                                           int(maxit), C.byref(lmu), L.ptr(lam), L.ptr(a0), L.ptr(beta),
                                           L.ptr(cvm), L.ptr(cvsd), C.byref(imin), C.byref(i1se), L.ptr(dev),
                                           C.byref(jerr)), "ate_cv_glmnet")
+        Lm = lmu.value
+        return dict(jerr=jerr.value, lmu=Lm, lambda_=lam[:Lm].copy(), a0=a0[:Lm].copy(),
+                    beta=np.ascontiguousarray(beta[:, :Lm]), cvm=cvm[:Lm].copy(), cvsd=cvsd[:Lm].copy(),
+                    idx_min=imin.value, idx_1se=i1se.value, dev_ratio=dev[:Lm].copy(),
+                    lambda_min=lam[imin.value], lambda_1se=lam[i1se.value])
+
+    def cv_glmnet_device(self, X_ptr, ld, n, p, foldid_ptr, nfolds=10, family="gaussian", penalty_factor=None,
+                         nlambda=100, thresh=1e-7, maxit=100000, shard_rank=0, shard_count=0):
+        """cv.glmnet on a device-resident row-major design [x | y | 1] (this rank's rows); see the header."""
+        vp = None if penalty_factor is None else L.f64(penalty_factor)
+        lmu = C.c_int()
+        imin = C.c_int()
+        i1se = C.c_int()
+        jerr = C.c_int()
+        lam = np.zeros(nlambda)
+        a0 = np.zeros(nlambda)
+        beta = np.zeros((p, nlambda), order="F")
+        cvm = np.zeros(nlambda)
+        cvsd = np.zeros(nlambda)
+        dev = np.zeros(nlambda)
+        fam = GAUSSIAN if family == "gaussian" else BINOMIAL
+        self._chk(self._lib.ate_cv_glmnet_device(self._h, fam, int(n), int(p), L.ptr(int(X_ptr)), int(ld),
+                                                 L.ptr(int(foldid_ptr)), int(nfolds), L.ptr(vp), int(nlambda),
+                                                 float(thresh), int(maxit), int(shard_rank), int(shard_count),
+                                                 C.byref(lmu), L.ptr(lam), L.ptr(a0), L.ptr(beta), L.ptr(cvm),
+                                                 L.ptr(cvsd), C.byref(imin), C.byref(i1se), L.ptr(dev), C.byref(jerr)),
+                  "ate_cv_glmnet_device")
         Lm = lmu.value
         return dict(jerr=jerr.value, lmu=Lm, lambda_=lam[:Lm].copy(), a0=a0[:Lm].copy(),
                     beta=np.ascontiguousarray(beta[:, :Lm]), cvm=cvm[:Lm].copy(), cvsd=cvsd[:Lm].copy(),
@@ -322,14 +350,18 @@ class Engine:
             y = L.f64(y)
             xp, wp, yp = L.ptr(x_base), L.ptr(w), L.ptr(y)
         K = o.K
-        fid = None if foldid is None else L.i32(foldid)
-        ips = None if inner_ps is None else L.i32(inner_ps)
-        iout = None if inner_out is None else L.i32(inner_out)
-        if ips is not None and ips.size != K * n:
-            raise ValueError("inner_ps must hold K*n fold ids")
-        bidx = None
-        if boot_idx is not None:
-            bidx = np.ascontiguousarray(boot_idx, dtype=np.int32)
+        if o.on_device:   # every input array is a device pointer, the fold ids and boot_idx included
+            fid, ips, iout = (None if a is None else int(a) for a in (foldid, inner_ps, inner_out))
+            bidx = None if boot_idx is None else int(boot_idx)
+        else:
+            fid = None if foldid is None else L.i32(foldid)
+            ips = None if inner_ps is None else L.i32(inner_ps)
+            iout = None if inner_out is None else L.i32(inner_out)
+            if ips is not None and ips.size != K * n:
+                raise ValueError("inner_ps must hold K*n fold ids")
+            bidx = None
+            if boot_idx is not None:
+                bidx = np.ascontiguousarray(boot_idx, dtype=np.int32)
         nuis = want_nuisances and not o.on_device
         phat = np.empty(n) if nuis else None
         m0 = np.empty(n) if nuis else None

@@ -58,19 +58,32 @@ ATE_API const char *ate_last_error(const ate_ctx *ctx);
 ATE_API void *ate_ctx_stream(const ate_ctx *ctx);
 /* Number of kernels this ctx has launched so far (bench.py's `gpu_launches`). */
 ATE_API long long ate_launch_count(const ate_ctx *ctx);
-/* Device time of the dominant kernel (weighted Gram) accumulated since the last reset, from
- * CUDA events recorded on the ctx stream around each launch: total ms and launch count.
- * Profiling must be switched on first; off by default. */
+/* Device time of the hot kernels accumulated since the last reset, from CUDA events recorded on the
+ * ctx stream around each launch: total ms, launch count, algorithmic flop and bytes.  `on`: 0 off
+ * (default), 1 the IRLS step kernel (irls_round_kernel), 2 the full-width Gram kernel
+ * (gram_dmma_kernel), 3 both. */
 ATE_API int ate_profile_enable(ate_ctx *ctx, int on);
 ATE_API int ate_profile_read(ate_ctx *ctx, double *gram_ms, long long *gram_launches, double *gram_flops,
                      double *gram_bytes);
 
-/* Multi-GPU hook (no reference counterpart: the reference is single-threaded).  When one fit is
- * shared by several ranks (ate_crossfit_opts.shard_count > 1) the library calls `fn` to sum a
- * small HOST buffer of doubles over all ranks (the paths of the full-data fits and the held-out
- * CV deviances of the cv-fold paths each rank solved; non-owners contribute zeros).  The R shim
- * would bind this to ncclAllReduce / MPI_Allreduce; bench.py binds it to torch.distributed.  Must
- * return 0 on success. */
+/* Multi-GPU (no reference counterpart: the reference is single-threaded).  When one fit is shared
+ * by several ranks (ate_crossfit_opts.shard_count > 1; one process and one ctx per GPU) every rank
+ * keeps a slice of the ROWS, and per-round partial sums -- the strong-set Grams, X^T r, X^T v and the
+ * deviances of every live path fit, the moment matrices of the gaussian fits, the held-out deviances --
+ * are summed over the ranks; the nuisances and the bootstrap replicates are all-gathered.
+ *
+ * ate_ctx_nccl_init: the library opens libnccl.so.2 itself and keeps an NCCL communicator in the
+ * ctx; every collective is then enqueued on the ctx stream between the kernels that produce and
+ * consume it (no host round trip).  Rank 0 obtains the 128-byte id with ate_nccl_unique_id and
+ * distributes it by whatever means the host program has (bench.py: torch.distributed broadcast; an R
+ * driver: Rmpi or a file), then every rank calls ate_ctx_nccl_init -- a collective call itself.
+ *
+ * ate_ctx_set_allreduce: the fallback when no communicator was created: the library calls `fn` to sum
+ * a HOST buffer of doubles over all ranks (one device->host->device round trip per collective).  Must
+ * return 0 on success.  Used by CPU-side tests with gloo and by hosts that only have MPI. */
+ATE_API int ate_nccl_unique_id(char *id128);
+ATE_API int ate_ctx_nccl_init(ate_ctx *ctx, const char *id128, int rank, int nranks);
+ATE_API int ate_ctx_nccl_destroy(ate_ctx *ctx);
 typedef int (*ate_allreduce_fn)(void *user, double *host_buf, long long count);
 ATE_API int ate_ctx_set_allreduce(ate_ctx *ctx, ate_allreduce_fn fn, void *user);
 
@@ -112,6 +125,21 @@ ATE_API int ate_cv_glmnet(ate_ctx *ctx, int family, long long n, int p, const do
                   int rng_kind, int nlambda, double thresh, int maxit, int *lmu, double *lambda,
                   double *a0, double *beta, double *cvm, double *cvsd, int *idx_min, int *idx_1se,
                   double *dev_ratio, int *jerr);
+
+/* The same cv.glmnet on data that already sits in HBM (the boundary is still ate_functions.R:101-103,
+ * :123-125, :139-141, :304-305; the host-matrix form above is what an R shim binds).  X_dev: THIS rank's
+ * rows of the library's row-major design, one record of ld doubles per observation laid out
+ * [x_1 .. x_p | y | 1 | 0 ...] (ld even, >= p + 2; 32-byte multiples stage fastest); foldid_dev: the
+ * fold ids of ALL n rows (device int32, the same on every rank).  shard_count <= 1: X_dev holds all
+ * n rows.  shard_count > 1: rank r holds rows [r c, min(n, (r + 1) c)), c = ceil(n / count) rounded up
+ * to a multiple of 4; the per-fold moment matrices (gaussian) or the per-round partial sums (binomial)
+ * are summed over the ranks inside the call and every rank returns the same model.  penalty_factor and
+ * all outputs are host arrays as in ate_cv_glmnet. */
+ATE_API int ate_cv_glmnet_device(ate_ctx *ctx, int family, long long n, int p, const double *X_dev, long long ld,
+                         const int32_t *foldid_dev, int nfolds, const double *penalty_factor, int nlambda,
+                         double thresh, int maxit, int shard_rank, int shard_count, int *lmu, double *lambda,
+                         double *a0, double *beta, double *cvm, double *cvsd, int *idx_min, int *idx_1se,
+                         double *dev_ratio, int *jerr);
 
 /* ---- f2: glm(formula, family = binomial("logit"))  (ate_functions.R:218-220, :231-234) ----- */
 /* The unpenalised logistic nuisance fits of doubly_robust_glm (and :156-158, Rmd:165-168):
@@ -170,7 +198,10 @@ ATE_API int ate_aipw_score_static(ate_ctx *ctx, long long n, const double *d_w, 
  * per replicate.  mode ATE_BOOT_PHILOX: indices are drawn on device; replicate b uses the
  * Philox stream keyed by (seed, rep_offset + b), so a replicate's value does not depend on how
  * replicates are sharded over GPUs.  boot[B] receives the replicate estimates and *se their
- * sd (n-1 denominator) -- pass se = NULL when sharding and combine boot[] yourself. */
+ * sd (n-1 denominator) -- pass se = NULL when sharding and combine boot[] yourself.  Index mode checks
+ * every index: one outside 1..n (R's NA_integer_ included) fails the call.  A host index matrix is
+ * streamed to the GPU in blocks of <= 256 MB (it is never resident as a whole); with on_device the
+ * five vectors AND idx are device pointers. */
 ATE_API int ate_bootstrap(ate_ctx *ctx, long long n, const double *w, const double *y, const double *p,
                   const double *m0, const double *m1, int B, int mode, const int32_t *idx,
                   uint64_t seed, long long rep_offset, double *boot, double *se, int on_device);
@@ -207,12 +238,13 @@ typedef struct ate_crossfit_opts {
     int boot_reps_here; /* replicates computed by this call (<= B; 0 = all B)                 */
     uint32_t r_seed;    /* seed for fold ids when foldid / inner ids are NULL                 */
     int rng_kind;       /* ATE_RNG_*                                                          */
-    int on_device;      /* x_base, w, y are device pointers                                   */
+    int on_device;      /* every array argument (x_base, w, y, the fold ids, boot_idx and the  */
+                        /*   nuisance outputs) is a device pointer                             */
     int fold_begin;     /* outer folds [fold_begin, fold_end) fitted by this call (1-based,   */
     int fold_end;       /*   0,0 = all); rows of other folds get 0 nuisances (shards can be summed) */
     int skip_score;     /* 1: stop after the nuisances (multi-GPU drivers combine first)      */
-    int shard_rank;     /* this process's rank and the number of ranks sharing ONE fit: the   */
-    int shard_count;    /*   propensity paths are dealt round-robin over ranks (0,0 = no sharding) */
+    int shard_rank;     /* this process's rank and the number of ranks sharing ONE fit (0,0 = */
+    int shard_count;    /*   none): rank r keeps rows [r c, (r + 1) c), c = ceil(n / count)   */
 } ate_crossfit_opts;
 
 ATE_API void ate_crossfit_default_opts(ate_crossfit_opts *o);
@@ -226,14 +258,22 @@ typedef struct ate_crossfit_result {
     double irls_solves;     /* total IRLS quadratic solves over all propensity path fits          */
     double strong_mean;     /* mean size of glmnet's strong set over those solves                 */
     double strong_frac2;    /* mean of (|strong| / p)^2: the share of Gram flops a solve needs    */
+    double ms_folds;        /* building the fold / row lists (device)                              */
+    double step_launches;   /* launches of the IRLS step kernel (one per lock-step round)          */
+    double row_fits;        /* sum over those launches and their live fits of the rows a fit saw    */
+    double rows_staged;     /* sum over those launches and their CTAs of the rows staged            */
+    double list_misses;     /* steps repeated because a column joined the strong set unpredicted    */
 } ate_crossfit_result;
 
 /* x_base[n*p0] col-major, w[n], y[n].  foldid[n] (1..K) and inner_ps / inner_out [K*n]
  * (row k: cv.glmnet fold ids of outer fold k's training rows in training-row order) may be
- * NULL => drawn with R's RNG from opts->r_seed in the order R would (k = 1..K: propensity
- * cv.glmnet then outcome cv.glmnet).  boot_idx: B*n for ATE_BOOT_INDEX, else NULL.
- * Outputs (host, may be NULL): phat, m0, m1 [n] stitched out-of-fold nuisances;
- * lambda_ps, lambda_out [K]; boot [B]. */
+ * NULL => drawn with R's RNG in the order R would (k = 1..K: propensity cv.glmnet then outcome
+ * cv.glmnet): whenever any ids are drawn the call does set.seed(opts->r_seed) first, so two
+ * identical calls draw identical folds.  boot_idx: B*n for ATE_BOOT_INDEX (replicate-major), else
+ * NULL.  Outputs (may be NULL): phat, m0, m1 [n] stitched out-of-fold nuisances (host, or device
+ * with on_device); lambda_ps, lambda_out [K] and boot [B] (always host).
+ * With shard_count > 1 (ate_ctx_nccl_init or ate_ctx_set_allreduce first) every rank passes the SAME
+ * full inputs, keeps its slice of the rows on its GPU, and receives the complete result. */
 ATE_API int ate_crossfit_aipw(ate_ctx *ctx, const ate_crossfit_opts *opts, long long n, int p0,
                       const double *x_base, const double *w, const double *y,
                       const int32_t *foldid, const int32_t *inner_ps, const int32_t *inner_out,
@@ -262,14 +302,18 @@ ATE_API int ate_cv_select(int nfolds, int lmu, const double *cvraw, const double
                           const int *fold_nlam, const double *lambda, double *cvm, double *cvsd,
                           int *idx_min, int *idx_1se);
 
-/* ---- introspection of the fused IRLS step's work plan (host only; no device call) --------- */
-/* No counterpart in the reference.  For a column list of `list_cols` columns (the strong set plus
- * candidates the binomial fit restricts its Gram to) returns how the 8x8 tiles of the Gram's lower
- * triangle are dealt to MMA warps: *ngroups CTAs per row chunk, *max_tiles on the busiest warp, and in
- * desc[2 * 128] one (x, y) pair per warp slot (8 slots per CTA): x = segment | count << 8, y = up to
- * four tile-row numbers, one per byte.  Lets tests check on a CPU-only box that every tile
- * is computed exactly once for every width.  Returns -1 for widths the step cannot take. */
-ATE_API int ate_step_plan_describe(int list_cols, int *ngroups, int *max_tiles, unsigned *desc);
+/* ---- introspection of the IRLS step kernel's work plan (host only; no device call) ------------- */
+/* No counterpart in the reference.  For `nfit` path fits of ONE cv.glmnet problem whose Gram column
+ * lists hold list_cols[f] columns (the strong set plus candidates), on a design that stages
+ * `staged_cols` columns per row, returns how the step kernel groups them into CTAs: the return value is
+ * the number of CTA kinds G (<= max_groups, else -2), and desc[24 g + ...] describes kind g:
+ *   [0] fits served (1 or 2), [1], [2] their indices, [3], [4] whether this kind evaluates the fit's
+ *   sums (a list too wide for one CTA is split over several kinds; the first one leads),
+ *   [8 + 2 w], [9 + 2 w] for MMA warp w = 0..7: x = fit slot | segment << 8 | count << 16, y = up to four
+ *   tile-row numbers, one per byte (count 0: the warp idles).
+ * Lets tests check on a CPU-only box that every 8x8 tile of every fit's lower triangle is computed
+ * exactly once for every mix of widths.  -1 for widths the step cannot take. */
+ATE_API int ate_round_plan_describe(int nfit, const int *list_cols, int staged_cols, int max_groups, unsigned *desc);
 
 #ifdef __cplusplus
 }

@@ -153,43 +153,65 @@ def test_gloo_exchange_between_ranks(tmp_path, world):
         assert p.returncode == 0, o
 
 
-def test_fused_step_work_plan_covers_every_tile_once_for_every_width():
-    """The fused IRLS step deals the 8x8 tiles of the list Gram's lower triangle to MMA warps from a
-    host-built plan (csrc/irls_step.cu).  For every list width it can take: each tile (r, c <= r) is
-    owned by exactly one warp, a warp holds <= 4 tile rows of ONE 32-column segment and <= 16 tiles,
-    the descriptors fit the launched grid, and narrow lists stay on warps 0-3 (one per SM
-    sub-partition)."""
-    from ate_replication_causalml_b200 import _lib
-    lib = _lib.load()
-    desc = (C.c_uint * 256)()
-    ng, mt = C.c_int(), C.c_int()
-    assert lib.ate_step_plan_describe(417, C.byref(ng), C.byref(mt), desc) == -1      # wider than the staging ring
-    for cols in range(0, 417):
-        assert lib.ate_step_plan_describe(cols, C.byref(ng), C.byref(mt), desc) == 0, cols
-        ntr = (cols + 7) // 8
-        owned = {}
-        busiest = 0
-        for k in range(128):
-            x, y = desc[2 * k], desc[2 * k + 1]
-            seg, cnt = x & 0xFF, (x >> 8) & 0xFF
+def _check_round_plan(lib, widths, staged):
+    """Every 8x8 tile of every fit's lower triangle is owned by exactly one MMA warp of one CTA kind; a CTA
+    kind serves at most two fits and each fit is evaluated (led) by exactly one kind."""
+    widths = np.asarray(widths, dtype=np.int32)
+    desc = (C.c_uint * (24 * 128))()
+    ng = lib.ate_round_plan_describe(len(widths), widths.ctypes.data_as(C.c_void_p), staged, 128, desc)
+    assert ng >= 1, (widths, ng)
+    owned = {}
+    leads = {}
+    for g in range(ng):
+        d = desc[24 * g: 24 * g + 24]
+        nfit = d[0]
+        assert 1 <= nfit <= 2
+        fits = [d[1 + s] for s in range(nfit)]
+        for s in range(nfit):
+            if d[3 + s]:
+                leads[fits[s]] = leads.get(fits[s], 0) + 1
+        for w in range(8):
+            x, y = d[8 + 2 * w], d[9 + 2 * w]
+            slot, seg, cnt = x & 0xFF, (x >> 8) & 0xFF, (x >> 16) & 0xFF
             if cnt == 0:
                 continue
-            assert k < 8 * ng.value and 1 <= cnt <= 4
+            assert slot < nfit and 1 <= cnt <= 4
+            f = fits[slot]
+            ntr = (int(widths[f]) + 7) // 8
             tiles = 0
             for u in range(cnt):
                 r = (y >> (8 * u)) & 0xFF
                 assert 4 * seg <= r < ntr
                 for n in range(min(4, r - 4 * seg + 1)):
-                    key = (r, 4 * seg + n)
-                    assert key not in owned, (cols, key)
-                    owned[key] = k
+                    key = (f, r, 4 * seg + n)
+                    assert key not in owned, (widths, key)
+                    owned[key] = (g, w)
                     tiles += 1
             assert tiles <= 16
-            busiest = max(busiest, tiles)
-        assert set(owned) == {(r, c) for r in range(ntr) for c in range(r + 1)}, cols
-        assert busiest == (mt.value if ntr else 0)
-        if 0 < cols <= 64:
-            assert ng.value == 1 and all(k % 8 < 4 for k in owned.values())
+    want = {(f, r, c) for f in range(len(widths)) for r in range((int(widths[f]) + 7) // 8) for c in range(r + 1)}
+    assert set(owned) == want, widths
+    assert all(leads.get(f, 0) == 1 for f in range(len(widths))), (widths, leads)
+    return ng
+
+
+def test_step_kernel_work_plan_covers_every_tile_once():
+    """The MMA warps of the IRLS step kernel compute the lower triangle of each fit's list Gram by a
+    host-built plan (csrc/irls_round.cu); checked here without a device for single fits of every
+    width, for the ten cv-fold fits of a problem, and for random mixes."""
+    from ate_replication_causalml_b200 import _lib
+    lib = _lib.load()
+    for cols in list(range(0, 130)) + [160, 200, 255, 256, 300, 412, 513, 1024]:
+        _check_round_plan(lib, [cols], 264)
+    assert _check_round_plan(lib, [64] * 10, 264) == 5           # two fits per CTA at the C1 width
+    assert _check_round_plan(lib, [64] * 10, 520) == 10          # wide rows (C4): one fit per CTA
+    assert _check_round_plan(lib, [200], 264) >= 2                # a list too wide for one CTA is split
+    rng = np.random.default_rng(3)
+    for _ in range(60):
+        k = int(rng.integers(1, 12))
+        _check_round_plan(lib, rng.integers(0, 180, k), 264)
+    desc = (C.c_uint * 24)()
+    bad = np.array([3000], dtype=np.int32)
+    assert lib.ate_round_plan_describe(1, bad.ctypes.data_as(C.c_void_p), 264, 1, desc) == -1
 
 
 def test_cv_select_is_cv_glmnets_summary():

@@ -241,9 +241,10 @@ def test_crossfit_on_belloni_design_with_twin_columns(engine, oracle):
     r2 = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], foldid=fo, inner_ps=ips, inner_out=iout,
                               n_continuous=d["n_continuous"], expand=2, B=0, thresh=1e-13)
     o2 = oracle.crossfit_aipw(xd, d["w"], d["y"], fo, ips, iout, thresh=1e-13)
-    if np.allclose(r2["lambda_ps"], o2["lambda_ps"], rtol=1e-9) and np.allclose(r2["lambda_out"], o2["lambda_out"], rtol=1e-9):
-        assert abs(r2["tau"] - o2["tau"]) <= 1e-6 * abs(o2["tau"])
-        assert abs(r2["se_sandwich"] - o2["se"]) <= 1e-6 * o2["se"]
+    assert np.allclose(r2["lambda_ps"], o2["lambda_ps"], rtol=1e-9) and np.allclose(r2["lambda_out"], o2["lambda_out"], rtol=1e-9)
+    assert np.abs(r2["phat"] - o2["phat"]).max() < 1e-6 and np.abs(r2["m1"] - o2["m1"]).max() < 1e-6
+    assert abs(r2["tau"] - o2["tau"]) <= 1e-6 * abs(o2["tau"])
+    assert abs(r2["se_sandwich"] - o2["se"]) <= 1e-6 * o2["se"]
 
 
 def test_crossfit_products_only_design_matches_expand_then_fit(engine, oracle):
@@ -265,12 +266,14 @@ def test_crossfit_device_pointers_equal_host_buffers(engine):
     n, p0 = 4000, 8
     d = _data(n, p0)
     fo, ips, iout = make_folds(n)
-    kw = dict(foldid=fo, inner_ps=ips, inner_out=iout, n_continuous=d["n_continuous"], expand=0, B=50, boot_mode=1, boot_seed=5)
-    h = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], **kw)
+    kw = dict(n_continuous=d["n_continuous"], expand=0, B=50, boot_mode=1, boot_seed=5)
+    h = engine.crossfit_aipw(d["x_raw"], d["w"], d["y"], foldid=fo, inner_ps=ips, inner_out=iout, **kw)
     dev = torch.device("cuda:0")
     xb = torch.from_numpy(np.asfortranarray(d["x_raw"]).T.copy()).to(dev)      # column-major n x p0
     w = torch.from_numpy(d["w"]).to(dev); y = torch.from_numpy(d["y"]).to(dev)
-    g = engine.crossfit_aipw(xb.data_ptr(), w.data_ptr(), y.data_ptr(), n=n, p0=p0, on_device=1, **kw)
+    fo_d, ips_d, iout_d = (torch.from_numpy(a).to(dev) for a in (fo, ips, iout))   # on_device: every array is a device pointer
+    g = engine.crossfit_aipw(xb.data_ptr(), w.data_ptr(), y.data_ptr(), n=n, p0=p0, on_device=1,
+                             foldid=fo_d.data_ptr(), inner_ps=ips_d.data_ptr(), inner_out=iout_d.data_ptr(), **kw)
     assert g["tau"] == h["tau"] and g["se_sandwich"] == h["se_sandwich"] and g["se_bootstrap"] == h["se_bootstrap"]
     assert torch.equal(xb, torch.from_numpy(np.asfortranarray(d["x_raw"]).T.copy()).to(dev))   # caller's buffer untouched
 

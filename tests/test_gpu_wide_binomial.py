@@ -56,7 +56,7 @@ def test_binomial_path_every_staged_width(engine, oracle, p, n):
 
 def test_binomial_path_with_lists_beyond_one_cta(engine, oracle):
     """A dense truth: late in the path the strong set passes 128 columns, so the list's Gram tiles no
-    longer fit one CTA's MMA warps and the work is split (ate_step_plan_describe: ngroups >= 2)."""
+    longer fit one CTA's MMA warps and the work is split (ate_round_plan_describe: ngroups >= 2)."""
     X, y = unique_product_design(12_000, 256, seed=77, dense=170)
     g = engine.glmnet(X, y, "binomial")
     o = oracle.glmnet(X, y, "binomial")

@@ -1,0 +1,58 @@
+#!/bin/bash
+# One gpurun call = a list of steps, each under its own timeout, each logging to gpurun_out/<tag>.log.
+# A failing step does not stop the session (a hung or trapped kernel kills only its own process).
+#   gpurun --timeout 1500 -- 'bash tools/gpu_session.sh probe tests bench'
+mkdir -p gpurun_out
+export PYTHONUNBUFFERED=1
+step() {  # tag, timeout seconds, command...
+    local tag=$1 to=$2; shift 2
+    local t0=$(date +%s)
+    timeout -k 10 "$to" "$@" > "gpurun_out/$tag.log" 2>&1
+    local rc=$?
+    echo "== $tag rc=$rc $(( $(date +%s) - t0 ))s"; tail -n 6 "gpurun_out/$tag.log" | cut -c1-400
+}
+for what in "$@"; do
+case $what in
+probe)
+    step probe_round 300 python tools/gpu_probe_round.py ;;
+sanitize)
+    PROBE_ONLY="n200" step sanitize_memcheck 600 compute-sanitizer --tool memcheck --print-limit 20 python tools/gpu_probe_round.py ;;
+kernels)
+    step t_kernels 600 python -m pytest tests/test_gpu_kernels.py -x -q ;;
+tests)
+    step t_kernels 600 python -m pytest tests/test_gpu_kernels.py -x -q
+    step t_paths 900 python -m pytest tests/test_gpu_paths.py -x -q
+    step t_glm 900 python -m pytest tests/test_gpu_glm_and_configs.py -x -q
+    step t_wide 900 python -m pytest tests/test_gpu_wide_binomial.py -x -q
+    step t_round2 900 python -m pytest tests/test_gpu_round2.py tests/test_zz_no_alloc.py -x -q ;;
+alltests)
+    step t_all 1500 python -m pytest tests -m gpu -x -q ;;
+smoke)
+    step smoke 300 python -c "import __graft_entry__ as g; g.smoke()" ;;
+bench)
+    ATE_TIMING=1 step bench_c1 900 python bench.py --steps 2 --warmup 2
+    grep -h '^{' gpurun_out/bench_c1.log | tail -1 > gpurun_out/bench_c1.json ;;
+benchq)
+    step bench_c1q 600 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e
+    grep -h '^{' gpurun_out/bench_c1q.log | tail -1 > gpurun_out/bench_c1q.json ;;
+ref)
+    step bench_ref 600 python bench.py --impl reference --steps 1 --warmup 1 --linearity
+    grep -h '^{' gpurun_out/bench_ref.log | tail -1 > gpurun_out/bench_ref.json ;;
+c2)
+    step bench_c2 600 python bench.py --workload C2 --steps 3 --warmup 3
+    grep -h '^{' gpurun_out/bench_c2.log | tail -1 > gpurun_out/bench_c2.json ;;
+c3)
+    step bench_c3 900 python bench.py --workload C3 --steps 2 --warmup 1
+    grep -h '^{' gpurun_out/bench_c3.log | tail -1 > gpurun_out/bench_c3.json ;;
+c4)
+    step bench_c4 1500 python bench.py --workload C4 --steps 1 --warmup 1 --no-e2e
+    grep -h '^{' gpurun_out/bench_c4.log | tail -1 > gpurun_out/bench_c4.json ;;
+ncu_list)
+    step ncu_launches 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --steps 1 --warmup 0 --n 200000 --no-cpu-baseline --no-e2e ;;
+ncu_round)
+    step ncu_round 900 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 150 -c 3 -o gpurun_out/ncu_round python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e ;;
+*)
+    echo "unknown step $what" ;;
+esac
+done
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,temperature.gpu,power.draw --format=csv,noheader
