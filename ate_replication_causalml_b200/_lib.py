@@ -96,6 +96,8 @@ SIGNATURES = {
     "ate_cv_select": (C.c_int, [C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int),
                                 C.POINTER(C.c_int)]),
     "ate_round_plan_describe": (C.c_int, [C.c_int, _vp, C.c_int, C.c_int, _vp]),
+    "ate_round_kernel_bench": (C.c_int, [_vp, c_ll, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         c_dp, c_dp, c_dp, C.POINTER(C.c_int)]),
     "ate_weighted_gram": (C.c_int, [_vp, c_ll, C.c_int, _vp, c_ll, _vp, _vp, c_ll, _vp, C.c_int]),
 }
 

@@ -45,6 +45,7 @@ struct ate_ctx {
     ate_allreduce_fn allreduce = nullptr;
     void *allreduce_user = nullptr;
     // multi-GPU: NCCL communicator owned by the ctx (comm.cu); collectives run on `stream`
+    int debug_skip = 0;  // ate_round_kernel_bench only: roles of the step kernel to idle
     void *nccl_comm = nullptr;
     int nccl_rank = 0, nccl_nranks = 1;
 };

@@ -31,6 +31,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <type_traits>
 #include <vector>
 
 #include "irls_round.cuh"
@@ -46,7 +47,7 @@ constexpr int R_THREADS = (R_CWARPS + R_PWARPS + R_HWARPS + R_EWARPS) * 32;
 constexpr int R_PRODUCER = R_CWARPS, R_HELPER = R_PRODUCER + R_PWARPS, R_EVAL = R_HELPER + R_HWARPS;
 constexpr int R_PAD = 4;
 constexpr int R_MAX_STAGES = 8;
-constexpr int R_FMAX = 2;  // fits served by one CTA
+constexpr int R_FMAX = 4;  // fits served by one CTA
 constexpr size_t R_SMEM_LIMIT = 227 * 1024;
 
 struct DProb {
@@ -80,6 +81,8 @@ struct RArgs {
     const DFit *fits;
     const DCta *ctas;
     int ncols, ni, iy, stages;
+    int wait_hint;  // ns of suspend-time hint for the barrier waits (0: plain try_wait)
+    int skip;  // measurement only (ate_round_kernel_bench): 1 MMA idle, 2 helpers idle, 4 eval without exp/log, 8 eval without dot
 };
 
 __device__ __forceinline__ unsigned long long gtimer_ns() {
@@ -87,20 +90,32 @@ __device__ __forceinline__ unsigned long long gtimer_ns() {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-// mbarrier wait that cannot hang the GPU: after ~4 s (a launch takes milliseconds) it traps
-__device__ __forceinline__ void wait_g(uint64_t *bar, uint32_t parity) {
+// mbarrier wait that cannot hang the GPU: after ~4 s (a launch takes milliseconds) it traps.  hint_ns > 0
+// passes try_wait a suspend-time hint (the warp sleeps in hardware until the phase completes or the time
+// is up); 0 uses the plain form, which re-issues the test after a short hardware-chosen wait.
+__device__ __forceinline__ void wait_g(uint64_t *bar, uint32_t parity, uint32_t hint_ns) {
     unsigned long long t0 = 0;
     for (unsigned spins = 1;; ++spins) {
         uint32_t done;
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(smem_u32(bar)), "r"(parity)
-            : "memory");
+        if (hint_ns) {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+                : "memory");
+        } else {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(smem_u32(bar)), "r"(parity)
+                : "memory");
+        }
         if (done) return;
-        if ((spins & 0xfffu) == 0) {
+        if (hint_ns || (spins & 0xfffu) == 0) {
             const unsigned long long t = gtimer_ns();
             if (t0 == 0)
                 t0 = t;
@@ -110,25 +125,55 @@ __device__ __forceinline__ void wait_g(uint64_t *bar, uint32_t parity) {
     }
 }
 
+// C(8x8) += A(8x4) * B(4x8) when `on` (a warp-uniform flag) is set.  The predicate sits on the MMA
+// itself, so the instruction stream has no branch around it (and no re-convergence barrier per tile).
+__device__ __forceinline__ void dmma884_if(int on, double &c0, double &c1, double a, double b) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.s32 p, %4, 0;\n\t"
+        "@p mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n\t}"
+        : "+d"(c0), "+d"(c1)
+        : "d"(a), "d"(b), "r"(on));
+}
+
+// -DATE_ROUND_TRACE: CTA 0 stamps clock64() per slot and role into a device buffer which
+// ate_round_kernel_bench writes to $ATE_ROUND_TRACE_OUT (tools/round_trace.py prints the timeline).
+#ifdef ATE_ROUND_TRACE
+constexpr int TR_SLOTS = 160, TR_EVENTS = 16;
+__device__ long long g_rtrace[TR_SLOTS * TR_EVENTS + 8];
+#define RTRACE(ev, it)                                                                          \
+    do {                                                                                        \
+        if (blockIdx.x == 0 && (it) < TR_SLOTS && (threadIdx.x & 31) == 0) g_rtrace[8 + (it) * TR_EVENTS + (ev)] = clock64(); \
+    } while (0)
+#else
+#define RTRACE(ev, it) do { } while (0)
+#endif
+
 template <int ROWS, int ITER, int FMAX, bool INIT>
 __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a) {
-    constexpr int HALVES = ROWS / 16;            // eval warps refresh 16 rows of a slot each
-    constexpr int TURNS = R_EWARPS / HALVES;     // ... and take turns on the slots
     constexpr int PSHARE = ROWS / R_PWARPS;      // rows of a slot staged by one producer (row-list mode)
-    constexpr int ITERH = (ITER + R_HWARPS - 1) / R_HWARPS;  // column pairs per helper lane
+    constexpr int ITERH = (ITER + 1) / 2;        // column pairs per lane of an FMA-pipe helper
+    constexpr bool HDMMA = !INIT && ITER <= 5;   // helpers on the DMMA pipe (rows up to 320 staged columns, not on the first step)
+    constexpr int HT = HDMMA ? (ITER * 8 + 1) / 2 : 1;  // column tiles per helper warp (two helpers: the most any gets)
+    constexpr int EWPS = ROWS / 8;               // eval warps per slot: each refreshes eight rows
+    constexpr int ETURNS = R_EWARPS / EWPS;      // ... and they take turns on the slots when a slot needs fewer than all four
     static_assert(ROWS == 16 || ROWS == 32, "slot geometry");
     static_assert(FMAX >= 1 && FMAX <= 4 && FMAX <= R_FMAX, "fits per CTA");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ DCta scta;
+    __shared__ int s_nk;
     const int ncols = a.ncols, pitch = ncols + R_PAD, stages = a.stages;
     const size_t stage_doubles = (size_t)ROWS * pitch;
     double *sx = reinterpret_cast<double *>(smem_raw);
     double *sv = sx + stage_doubles * stages;           // [stages][FMAX][ROWS]: v of every fit
     double *sr = sv + (size_t)stages * FMAX * ROWS;     // [stages][FMAX][ROWS]: r of every fit
-    uint64_t *full = reinterpret_cast<uint64_t *>(sr + (size_t)stages * FMAX * ROWS);
+    double *sbeta = sr + (size_t)stages * FMAX * ROWS;  // [FMAX][ncols]: coefficients of every fit (zero beyond ni)
+    int *skk = reinterpret_cast<int *>(sbeta + (size_t)FMAX * ncols);  // the 4-column steps in which some coefficient is non-zero
+    uint64_t *full = reinterpret_cast<uint64_t *>(skk + ((ncols / 4 + 3) & ~1));
     uint64_t *vfull = full + stages, *empty = vfull + stages;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t whint = (uint32_t)a.wait_hint;
     if (threadIdx.x < (int)(sizeof(DCta) / sizeof(int)))
         reinterpret_cast<int *>(&scta)[threadIdx.x] = reinterpret_cast<const int *>(a.ctas + blockIdx.x)[threadIdx.x];
     __syncthreads();
@@ -137,34 +182,61 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
     const int nit = (int)((c_end - c_begin + ROWS - 1) / ROWS);
     const int nfit = scta.nfit;
     const bool contiguous = (prob.rows == nullptr && prob.ld == (long long)pitch);
+    // warp roles: 0-7 MMA, 8 producer, 9 second producer (row-list mode) or third helper, 10-11 helpers, 12-15 eval
+    const int nhelp = contiguous ? 3 : 2;
+    const bool is_producer = (warp == R_PRODUCER) || (warp == R_PRODUCER + 1 && !contiguous);
+    const int hidx = (warp == R_HELPER) ? 0 : (warp == R_HELPER + 1) ? 1 : (warp == R_PRODUCER + 1 && contiguous) ? 2 : -1;
 
     for (int e = threadIdx.x; e < stages * ROWS * R_PAD; e += blockDim.x)
         sx[(size_t)(e / R_PAD) * pitch + ncols + (e % R_PAD)] = 0.0;  // the list's "zero column"
+    for (int e = threadIdx.x; e < FMAX * ncols; e += blockDim.x) {
+        const int f = e / ncols, c = e - f * ncols;
+        sbeta[e] = (f < nfit && c < a.ni) ? a.fits[scta.fit[f]].coef[c] : 0.0;
+    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(full + s, contiguous ? 1 : R_PWARPS);
-            mbar_init(vfull + s, HALVES);
-            mbar_init(empty + s, R_CWARPS + R_HWARPS + R_EWARPS);  // EVERY consumer warp, every slot
+            mbar_init(vfull + s, EWPS);
+            mbar_init(empty + s, R_CWARPS + nhelp + R_EWARPS);  // EVERY consumer warp, every slot
         }
         mbar_fence_init();
+    }
+    __syncthreads();
+    if (warp == 0) {
+        // the steps of four columns in which at least one fit has a non-zero coefficient: eta needs no others
+        int nk = 0;
+        const int nks = ncols >> 2;
+        for (int k0 = 0; k0 < nks; k0 += 32) {
+            const int kk = k0 + lane;
+            bool any = false;
+            if (kk < nks)
+#pragma unroll
+                for (int f = 0; f < FMAX; ++f)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) any |= (sbeta[f * ncols + 4 * kk + c] != 0.0);
+            const unsigned m = __ballot_sync(0xffffffffu, any);
+            if (any) skk[nk + __popc(m & ((1u << lane) - 1u))] = kk;
+            nk += __popc(m);
+        }
+        if (lane == 0) s_nk = nk;
     }
     __syncthreads();
     // Ring protocol: every consumer warp visits every slot in order and arrives on `empty` for it,
     // whether or not it has work there, and every producer waits on `empty` for every slot: no
     // barrier can complete a phase that one of its waiters has not seen the previous phase of.
 
-    if (warp >= R_PRODUCER && warp < R_PRODUCER + R_PWARPS) {
+    if (is_producer) {
         // ------------------------------ producers ------------------------------
         const int pw = warp - R_PRODUCER;
         if (contiguous) {
-            if (pw != 0) return;
             const uint32_t rowb = (uint32_t)pitch * 8u;
             for (int it = 0; it < nit; ++it) {
                 const int s = it % stages;
                 const uint32_t ph = (uint32_t)(it / stages) & 1u;
                 const long long t0 = c_begin + (long long)it * ROWS;
                 const int cnt = (int)((c_end - t0) < ROWS ? (c_end - t0) : ROWS);
-                wait_g(empty + s, ph ^ 1u);
+                wait_g(empty + s, ph ^ 1u, whint);
+                RTRACE(0, it);  // producer: slot free
                 double *dst0 = sx + stage_doubles * s;
                 if (lane < ROWS && lane >= cnt)  // a short last slot: the missing rows read as zeros
                     for (int c = 0; c < ncols; ++c) dst0[(size_t)lane * pitch + c] = 0.0;
@@ -204,7 +276,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
                     ring_ok[d] = fetch(it + PF, ring_r[d]);
                     const int s = it % stages;
                     const uint32_t ph = (uint32_t)(it / stages) & 1u;
-                    wait_g(empty + s, ph ^ 1u);
+                    wait_g(empty + s, ph ^ 1u, whint);
                     double *dst = sx + stage_doubles * s + (size_t)myrow * pitch;
                     if (lane < PSHARE && !cur_ok)
                         for (int c = 0; c < ncols; ++c) dst[c] = 0.0;
@@ -218,23 +290,19 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         }
     } else if (warp >= R_EVAL) {
         // ------------------------------ evaluation ------------------------------
+        // eta of eight rows for every fit of the CTA is one 8 x 8 DMMA accumulation: A = the eight staged
+        // rows, four consecutive columns per step (conflict-light loads, the same for all fits), B = the
+        // fits' coefficients in shared memory.  Only the steps in which some coefficient is non-zero are
+        // taken (a few dozen of ncols / 4 on a lasso path).  One shuffle then hands lane (row g, k4) the eta
+        // of fit k4, and exp / divide / log run once per lane whatever the number of fits.
+        // v and r are published (and the slot released) BEFORE the log of the deviance is taken.
         const int e = warp - R_EVAL;
-        const int half = e % HALVES, turn = e / HALVES;
         const int ni = a.ni;
-        double beta[FMAX][2 * ITER];
-#pragma unroll
-        for (int f = 0; f < FMAX; ++f) {
-            const double *cf = f < nfit ? a.fits[scta.fit[f]].coef : nullptr;
-#pragma unroll
-            for (int i = 0; i < ITER; ++i) {
-                const int c = 2 * lane + 64 * i;
-                beta[f][2 * i] = (cf && c < ni) ? cf[c] : 0.0;
-                beta[f][2 * i + 1] = (cf && c + 1 < ni) ? cf[c + 1] : 0.0;
-            }
-        }
-        // the four lanes of a row group finish one fit each
-        const int fsel = lane & 3;
+        const int grp = e % EWPS, turn = e / EWPS;
+        const int g = lane >> 2, k4 = lane & 3;
+        const int fsel = k4;
         const bool mine = fsel < nfit && fsel < FMAX;
+        const double pmin = GLM_PMIN, fmax_ = log(1.0 / pmin - 1.0), fmin_ = -fmax_;
         double a0 = 0.0, w = 0.0;
         long long hb = 0, he = 0;
         bool lead = false;
@@ -246,91 +314,84 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             he = ft.hole_begin + ft.hole_len;
             lead = scta.lead[fsel] != 0;
         }
-        const double pmin = GLM_PMIN, fmax_ = log(1.0 / pmin - 1.0), fmin_ = -fmax_;
         double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0;
+        const int r0 = 8 * grp, rr = r0 + g;
+        const int nk = (a.skip & 8) ? 0 : s_nk;
+        const bool bok = g < FMAX;
+        const double *brow = sbeta + (size_t)(bok ? g : 0) * ncols + k4;
+        const int src_lane = (lane & ~3) | (k4 >> 1);
         for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
-            wait_g(full + s, ph);
-            if ((it % TURNS) != turn) {  // not this warp's slot: release it at once
+            wait_g(full + s, ph, whint);
+            if ((it % ETURNS) != turn) {  // not this warp's slot: release it at once
                 if (lane == 0) mbar_arrive(empty + s);
                 continue;
             }
+            RTRACE(1 + (grp & 1), it);  // eval warp of group 0 / 1: rows landed
             const double *slot = sx + stage_doubles * s;
-#pragma unroll 1
-            for (int grp = 0; grp < 2; ++grp) {
-                const int r0 = 16 * half + 8 * grp;
-                double part[FMAX][8];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const double *rowp = slot + (size_t)(r0 + q) * pitch;
-#pragma unroll
-                    for (int f = 0; f < FMAX; ++f) part[f][q] = 0.0;
-#pragma unroll
-                    for (int i = 0; i < ITER; ++i) {
-                        const int c = 2 * lane + 64 * i;
-                        if (c < ncols) {
-                            const double2 t2 = *reinterpret_cast<const double2 *>(rowp + c);
-#pragma unroll
-                            for (int f = 0; f < FMAX; ++f)
-                                if (f < nfit)
-                                    part[f][q] = fma(t2.x, beta[f][2 * i], fma(t2.y, beta[f][2 * i + 1], part[f][q]));
-                        }
-                    }
-                }
-                // reduce-scatter the 8 partial dots of every fit: lane l ends with row l >> 2
-#pragma unroll
-                for (int f = 0; f < FMAX; ++f) {
-#pragma unroll
-                    for (int hf = 4, off = 16; hf >= 1; hf >>= 1, off >>= 1) {
-                        const bool up = (lane & off) != 0;
-#pragma unroll
-                        for (int k = 0; k < hf; ++k) {
-                            const double send = up ? part[f][k] : part[f][k + hf], keep = up ? part[f][k + hf] : part[f][k];
-                            part[f][k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-                        }
-                    }
-                    part[f][0] += __shfl_xor_sync(0xffffffffu, part[f][0], 2);
-                    part[f][0] += __shfl_xor_sync(0xffffffffu, part[f][0], 1);
-                }
-                double dot = part[0][0];
-#pragma unroll
-                for (int f = 1; f < FMAX; ++f)
-                    if (fsel == f) dot = part[f][0];
-                const int rr = r0 + (lane >> 2);
-                const long long t = c_begin + (long long)it * ROWS + rr;
-                const bool valid = mine && t < c_end && !(t >= hb && t < he);
-                const double yi = slot[(size_t)rr * pitch + a.iy];
-                const double fi = a0 + dot;
-                double q;
-                if (fi < fmin_)
-                    q = 0.0;
-                else if (fi > fmax_)
-                    q = 1.0;
-                else
-                    q = 1.0 / (1.0 + exp(-fi));
-                const double vi = valid ? w * q * (1.0 - q) : 0.0, ri = valid ? w * (yi - q) : 0.0;
-                if (mine) {
-                    sv[((size_t)s * FMAX + fsel) * ROWS + rr] = vi;
-                    sr[((size_t)s * FMAX + fsel) * ROWS + rr] = ri;
-                }
-                if (lead && valid) {
-                    const double qc = fmin(fmax(q, pmin), 1.0 - pmin);
-                    s_xmz += vi;
-                    s_sr += ri;
-                    // y is 0/1 on this path, so one of the two log terms vanishes
-                    const double ll = (yi == 1.0) ? log(qc) : (yi == 0.0) ? log(1.0 - qc)
-                                                            : yi * log(qc) + (1.0 - yi) * log(1.0 - qc);
-                    s_dev -= w * ll;
-                }
+            const double *arow = slot + (size_t)rr * pitch + k4;
+            double c0 = 0.0, c1 = 0.0, d0 = 0.0, d1 = 0.0;  // two accumulation chains
+            int j = 0;
+#pragma unroll 2
+            for (; j + 1 < nk; j += 2) {
+                const int ka = skk[j] << 2, kb = skk[j + 1] << 2;
+                dmma884(c0, c1, arow[ka], bok ? brow[ka] : 0.0);
+                dmma884(d0, d1, arow[kb], bok ? brow[kb] : 0.0);
+            }
+            if (j < nk) {
+                const int ka = skk[j] << 2;
+                dmma884(c0, c1, arow[ka], bok ? brow[ka] : 0.0);
+            }
+            c0 += d0;
+            c1 += d1;
+            // lane (g, k4) holds fits 2 k4 and 2 k4 + 1 of row g; hand fit k4 to lane (g, k4)
+            const double v0 = __shfl_sync(0xffffffffu, c0, src_lane), v1 = __shfl_sync(0xffffffffu, c1, src_lane);
+            const double dot = (k4 & 1) ? v1 : v0;
+            const long long t = c_begin + (long long)it * ROWS + rr;
+            const bool valid = mine && t < c_end && !(t >= hb && t < he);
+            const double yi = slot[(size_t)rr * pitch + a.iy];
+            const double fi = a0 + dot;
+            double q;
+            if (a.skip & 4)
+                q = 0.5 + 1e-3 * fi;
+            else if (fi < fmin_)
+                q = 0.0;
+            else if (fi > fmax_)
+                q = 1.0;
+            else
+                q = 1.0 / (1.0 + exp(-fi));
+            const double vi = valid ? w * q * (1.0 - q) : 0.0, ri = valid ? w * (yi - q) : 0.0;
+            if (mine) {
+                sv[((size_t)s * FMAX + fsel) * ROWS + rr] = vi;
+                sr[((size_t)s * FMAX + fsel) * ROWS + rr] = ri;
             }
             __syncwarp();
+            RTRACE(3 + (grp & 1), it);  // eval: v, r published
             if (lane == 0) {
                 mbar_arrive(vfull + s);  // MMA and helper warps may start on this slot
                 mbar_arrive(empty + s);  // ... and this warp is done with its staged rows
             }
+            if (!(a.skip & 4)) {
+                // log-likelihood term, off the slot's critical path.  y is 0/1 on this path, so one of the
+                // two log terms vanishes: ONE log per lane, evaluated by all lanes together; a non-binary
+                // response takes the general form
+                const double qc = fmin(fmax(q, pmin), 1.0 - pmin);
+                const bool count = lead && valid;
+                const bool binary = (yi == 0.0 || yi == 1.0);
+                double ll;
+                if (__all_sync(0xffffffffu, binary || !count))
+                    ll = log(yi == 1.0 ? qc : 1.0 - qc);
+                else
+                    ll = yi * log(qc) + (1.0 - yi) * log(1.0 - qc);
+                if (count) {
+                    s_xmz += vi;
+                    s_sr += ri;
+                    s_dev -= w * ll;
+                }
+            }
         }
-        // lanes with the same fsel hold partial sums of the same fit
+        // lanes with the same k4 hold partial sums of the same fit
 #pragma unroll
         for (int o = 16; o >= 4; o >>= 1) {
             s_xmz += __shfl_xor_sync(0xffffffffu, s_xmz, o);
@@ -343,83 +404,124 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             ep[1] = s_sr;
             ep[2] = s_dev;
         }
-    } else if (warp >= R_HELPER) {
+    } else if (hidx >= 0) {
         // ------------------------------ helpers: X^T r, X^T v (and sum v x^2 on the first step) -----
-        const int h = warp - R_HELPER;
+        const int h = hidx;
         const int ni = a.ni;
-        const int npairs = ncols >> 1, ppw = (npairs + R_HWARPS - 1) / R_HWARPS;
         bool any_lead = false;
 #pragma unroll
         for (int f = 0; f < FMAX; ++f) any_lead |= (f < nfit && scta.lead[f] != 0);
-        double gr[FMAX][2 * ITERH], hx[FMAX][2 * ITERH], hxx[INIT ? FMAX : 1][INIT ? 2 * ITERH : 1];
+        if constexpr (HDMMA) {
+            // [r_0 v_0 r_1 v_1 ...]^T X on the DMMA pipe: the eight rows of A are (fit, r | v) pairs, a tile
+            // of B is four staged rows x eight CONSECUTIVE columns (conflict-free loads), so one DMMA per
+            // tile and k-step serves X^T r and X^T v of up to four fits.  The column tiles are split
+            // between the helper warps (three when one producer suffices, else two).
+            const int ntile = ncols >> 3, tpw = (ntile + nhelp - 1) / nhelp;
+            const int tile0 = h * tpw;
+            int nmy = ntile - tile0;
+            nmy = nmy < 0 ? 0 : (nmy > tpw ? tpw : nmy);
+            const int g = lane >> 2, k4 = lane & 3;
+            const int af = g >> 1;               // the fit whose r (g even) or v (g odd) this lane feeds into A
+            const bool a_ok = af < nfit && af < FMAX;
+            double acc[HT][2];
 #pragma unroll
-        for (int f = 0; f < FMAX; ++f)
+            for (int t = 0; t < HT; ++t) acc[t][0] = acc[t][1] = 0.0;
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % stages;
+                const uint32_t ph = (uint32_t)(it / stages) & 1u;
+                wait_g(full + s, ph, whint);
+                if (any_lead && !(a.skip & 2)) {
+                    wait_g(vfull + s, ph, whint);
+                    if (h < 2) RTRACE(5 + h, it);  // helper h: start
+                    const double *slot = sx + stage_doubles * s;
+                    const double *srcA = ((g & 1) ? sv : sr) + ((size_t)s * FMAX + (a_ok ? af : 0)) * ROWS;
+#pragma unroll 1
+                    for (int kk = 0; kk < ROWS / 4; ++kk) {
+                        const int r = kk * 4 + k4;
+                        const double av = a_ok ? srcA[r] : 0.0;
+                        const double *rowp = slot + (size_t)r * pitch + tile0 * 8 + g;
+#pragma unroll
+                        for (int t = 0; t < HT; ++t)
+                            if (t < nmy) dmma884(acc[t][0], acc[t][1], av, rowp[t * 8]);
+                    }
+                }
+                __syncwarp();
+                if (h < 2) RTRACE(7 + h, it);  // helper h: done
+                if (lane == 0) mbar_arrive(empty + s);
+            }
+            // C[m][n]: lane (g, k4) holds m = g (fit g / 2, r | v), columns 8 (tile0 + t) + 2 k4 + {0, 1}
+            if (a_ok && scta.lead[af] != 0) {
+                double *ep = a.fits[scta.fit[af]].eval_part + (size_t)scta.chunk * (3 * ni + 3 * R_EWARPS) + ((g & 1) ? ni : 0);
+#pragma unroll
+                for (int t = 0; t < HT; ++t)
+                    if (t < nmy) {
+                        const int c = (tile0 + t) * 8 + 2 * k4;
+                        if (c < ni) ep[c] = acc[t][0];
+                        if (c + 1 < ni) ep[c + 1] = acc[t][1];
+                    }
+            }
+        } else {
+            // FMA-pipe form (first step of a fit, and rows wider than 320 columns; one fit per CTA there):
+            // lanes own column pairs, the columns are split between the helper warps
+            static_assert(HDMMA || FMAX == 1, "the FMA-pipe helper serves one fit");
+            const int npairs = ncols >> 1, ppw = (npairs + nhelp - 1) / nhelp;
+            double gr[2 * ITERH], hx[2 * ITERH], hxx[INIT ? 2 * ITERH : 1];
 #pragma unroll
             for (int i = 0; i < 2 * ITERH; ++i) {
-                gr[f][i] = hx[f][i] = 0.0;
-                if (INIT) hxx[f][i] = 0.0;
+                gr[i] = hx[i] = 0.0;
+                if (INIT) hxx[i] = 0.0;
             }
-        int col[ITERH];
+            int col[ITERH];
 #pragma unroll
-        for (int i = 0; i < ITERH; ++i) {
-            const int idx = lane + 32 * i;
-            col[i] = (idx < ppw && h * ppw + idx < npairs) ? 2 * (h * ppw + idx) : -1;
-        }
-        for (int it = 0; it < nit; ++it) {
-            const int s = it % stages;
-            const uint32_t ph = (uint32_t)(it / stages) & 1u;
-            wait_g(full + s, ph);
-            if (any_lead) {
-                wait_g(vfull + s, ph);
-                const double *slot = sx + stage_doubles * s;
+            for (int i = 0; i < ITERH; ++i) {
+                const int idx = lane + 32 * i;
+                col[i] = (idx < ppw && h * ppw + idx < npairs) ? 2 * (h * ppw + idx) : -1;
+            }
+            for (int it = 0; it < nit; ++it) {
+                const int s = it % stages;
+                const uint32_t ph = (uint32_t)(it / stages) & 1u;
+                wait_g(full + s, ph, whint);
+                if (any_lead && !(a.skip & 2)) {
+                    wait_g(vfull + s, ph, whint);
+                    const double *slot = sx + stage_doubles * s;
 #pragma unroll 2
-                for (int r = 0; r < ROWS; ++r) {
-                    const double *rowp = slot + (size_t)r * pitch;
-                    double2 x[ITERH];
+                    for (int r = 0; r < ROWS; ++r) {
+                        const double *rowp = slot + (size_t)r * pitch;
+                        const double vj = sv[(size_t)s * FMAX * ROWS + r];
+                        const double rj = sr[(size_t)s * FMAX * ROWS + r];
 #pragma unroll
-                    for (int i = 0; i < ITERH; ++i)
-                        x[i] = col[i] >= 0 ? *reinterpret_cast<const double2 *>(rowp + col[i]) : make_double2(0.0, 0.0);
-#pragma unroll
-                    for (int f = 0; f < FMAX; ++f) {
-                        if (f < nfit) {
-                            const double vj = sv[((size_t)s * FMAX + f) * ROWS + r];
-                            const double rj = sr[((size_t)s * FMAX + f) * ROWS + r];
-#pragma unroll
-                            for (int i = 0; i < ITERH; ++i) {
-                                gr[f][2 * i] = fma(rj, x[i].x, gr[f][2 * i]);
-                                gr[f][2 * i + 1] = fma(rj, x[i].y, gr[f][2 * i + 1]);
-                                hx[f][2 * i] = fma(vj, x[i].x, hx[f][2 * i]);
-                                hx[f][2 * i + 1] = fma(vj, x[i].y, hx[f][2 * i + 1]);
-                                if (INIT) {
-                                    hxx[f][2 * i] = fma(vj * x[i].x, x[i].x, hxx[f][2 * i]);
-                                    hxx[f][2 * i + 1] = fma(vj * x[i].y, x[i].y, hxx[f][2 * i + 1]);
-                                }
+                        for (int i = 0; i < ITERH; ++i) {
+                            const double2 x = col[i] >= 0 ? *reinterpret_cast<const double2 *>(rowp + col[i]) : make_double2(0.0, 0.0);
+                            gr[2 * i] = fma(rj, x.x, gr[2 * i]);
+                            gr[2 * i + 1] = fma(rj, x.y, gr[2 * i + 1]);
+                            hx[2 * i] = fma(vj, x.x, hx[2 * i]);
+                            hx[2 * i + 1] = fma(vj, x.y, hx[2 * i + 1]);
+                            if (INIT) {
+                                hxx[2 * i] = fma(vj * x.x, x.x, hxx[2 * i]);
+                                hxx[2 * i + 1] = fma(vj * x.y, x.y, hxx[2 * i + 1]);
                             }
                         }
                     }
                 }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty + s);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(empty + s);
-        }
-#pragma unroll
-        for (int f = 0; f < FMAX; ++f) {
-            if (f < nfit && scta.lead[f] != 0) {
-                double *ep = a.fits[scta.fit[f]].eval_part + (size_t)scta.chunk * (3 * ni + 3 * R_EWARPS);
+            if (nfit > 0 && scta.lead[0] != 0) {
+                double *ep = a.fits[scta.fit[0]].eval_part + (size_t)scta.chunk * (3 * ni + 3 * R_EWARPS);
 #pragma unroll
                 for (int i = 0; i < ITERH; ++i)
 #pragma unroll
                     for (int hh = 0; hh < 2; ++hh) {
                         const int c = col[i] + hh;
                         if (col[i] >= 0 && c < ni) {
-                            ep[c] = gr[f][2 * i + hh];
-                            ep[ni + c] = hx[f][2 * i + hh];
-                            if (INIT) ep[2 * ni + c] = hxx[f][2 * i + hh];
+                            ep[c] = gr[2 * i + hh];
+                            ep[ni + c] = hx[2 * i + hh];
+                            if (INIT) ep[2 * ni + c] = hxx[2 * i + hh];
                         }
                     }
             }
         }
-    } else {
+    } else if (warp < R_CWARPS) {
         // ------------------------------ MMA ------------------------------
         const uint2 d = scta.mma[warp];
         const int fs = (int)(d.x & 0xffu), seg = (int)((d.x >> 8) & 0xffu), cnt = (int)((d.x >> 16) & 0xffu);
@@ -442,29 +544,40 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
-            wait_g(full + s, ph);
-            if (cnt > 0) {
-                wait_g(vfull + s, ph);
+            wait_g(full + s, ph, whint);
+            if (cnt > 0 && !(a.skip & 1)) {
+                wait_g(vfull + s, ph, whint);
+                if (warp < 3) RTRACE(9 + 2 * warp, it);  // MMA warp 0..2: start
                 const double *base = sx + stage_doubles * s;
                 const double *vs = sv + ((size_t)s * FMAX + fs) * ROWS;
-#pragma unroll
+#pragma unroll 1
                 for (int kk = 0; kk < ROWS / 4; ++kk) {
                     const int r = kk * 4 + k4;
                     const double *rowp = base + (size_t)r * pitch;
                     const double vv = vs[r];
-                    double fa[4], fb[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) fa[u] = nt[u] > 0 ? rowp[offA[u]] : 0.0;
+                    double fb[4];
 #pragma unroll
                     for (int n = 0; n < 4; ++n) fb[n] = rowp[offB[n]] * vv;
+                    // nt[u] is the same in every lane: the branches below are uniform, and only the tiles
+                    // the warp owns cost an instruction
 #pragma unroll
-                    for (int u = 0; u < 4; ++u)
-#pragma unroll
-                        for (int n = 0; n < 4; ++n)
-                            if (n < nt[u]) dmma884(acc[u][n][0], acc[u][n][1], fa[u], fb[n]);
+                    for (int u = 0; u < 4; ++u) {
+                        if (nt[u] > 0) {
+                            const double fa = rowp[offA[u]];
+                            dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
+                            if (nt[u] > 1) {
+                                dmma884(acc[u][1][0], acc[u][1][1], fa, fb[1]);
+                                if (nt[u] > 2) {
+                                    dmma884(acc[u][2][0], acc[u][2][1], fa, fb[2]);
+                                    if (nt[u] > 3) dmma884(acc[u][3][0], acc[u][3][1], fa, fb[3]);
+                                }
+                            }
+                        }
+                    }
                 }
             }
             __syncwarp();
+            if (warp < 3) RTRACE(10 + 2 * warp, it);  // MMA warp 0..2: done
             if (lane == 0) mbar_arrive(empty + s);
         }
         // tile (tr[u], 4 seg + n) sits in 32x32 block (tr[u] / 4, seg) of the fold kernel's layout
@@ -558,7 +671,7 @@ void pack_bins(int ntr, int T, std::vector<Bin> &out) {
 
 struct Group {
     int prob = 0;
-    int nfit = 0, fit[R_FMAX] = {0, 0}, lead[R_FMAX] = {0, 0};
+    int nfit = 0, fit[R_FMAX] = {0, 0, 0, 0}, lead[R_FMAX] = {0, 0, 0, 0};
     std::vector<std::pair<int, Bin>> bins;  // (fit slot, bin), <= R_CWARPS
     int tiles = 0;
     double cost = 0.0;
@@ -646,11 +759,25 @@ template <int ROWS, int ITER, int FMAX>
 int launch_round(ate_ctx *ctx, const RArgs &a, int nctas, size_t smem, bool init) {
     if (init) {
         auto k = irls_round_kernel<ROWS, ITER, FMAX, true>;
-        if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R_SMEM_LIMIT) != cudaSuccess) return -1;
+        if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
         k<<<nctas, R_THREADS, smem, ctx->stream>>>(a);
     } else {
         auto k = irls_round_kernel<ROWS, ITER, FMAX, false>;
-        if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)R_SMEM_LIMIT) != cudaSuccess) return -1;
+        if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        k<<<nctas, R_THREADS, smem, ctx->stream>>>(a);
+    }
+    return 0;
+}
+// narrow rows: a fit's first step runs one fit per CTA on the FMA-pipe helpers, every other step four
+template <int ROWS, int ITER>
+int launch_narrow(ate_ctx *ctx, const RArgs &a, int nctas, size_t smem, bool init) {
+    if (init) {
+        auto k = irls_round_kernel<ROWS, ITER, 1, true>;
+        if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        k<<<nctas, R_THREADS, smem, ctx->stream>>>(a);
+    } else {
+        auto k = irls_round_kernel<ROWS, ITER, R_FMAX, false>;
+        if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
         k<<<nctas, R_THREADS, smem, ctx->stream>>>(a);
     }
     return 0;
@@ -658,10 +785,11 @@ int launch_round(ate_ctx *ctx, const RArgs &a, int nctas, size_t smem, bool init
 
 }  // namespace
 
+static int round_fmax(int ncs, int init);
 // host-only introspection of the planner (include/ate_b200.h)
 extern "C" int ate_round_plan_describe(int nfit, const int *list_cols, int staged_cols, int max_groups, unsigned *desc) {
     if (nfit < 1 || !list_cols || !desc || max_groups < 1 || staged_cols < 8) return -1;
-    const int fmax = (staged_cols + 63) / 64 <= 5 ? R_FMAX : 1;
+    const int fmax = round_fmax(staged_cols, 0);
     std::vector<int> prob_of(nfit, 0), live(nfit, 1), nGs(list_cols, list_cols + nfit);
     std::vector<Group> groups;
     if (build_groups(1, prob_of, live, nGs, fmax, groups) < 0) return -1;
@@ -673,7 +801,7 @@ extern "C" int ate_round_plan_describe(int nfit, const int *list_cols, int stage
         d[0] = (unsigned)g.nfit;
         for (int sl = 0; sl < g.nfit; ++sl) {
             d[1 + sl] = (unsigned)g.fit[sl];
-            d[3 + sl] = (unsigned)g.lead[sl];
+            d[5] |= (unsigned)(g.lead[sl] ? 1 : 0) << sl;
         }
         for (size_t b = 0; b < g.bins.size(); ++b) {
             d[8 + 2 * b] = bin_x(g.bins[b].first, g.bins[b].second);
@@ -684,10 +812,17 @@ extern "C" int ate_round_plan_describe(int nfit, const int *list_cols, int stage
 }
 
 // slot geometry for a staged width: 32-row slots while three of them fit, else 16-row slots
-static int round_rows_for(int ncs) {
-    const size_t b32 = sizeof(double) * ((size_t)32 * (ncs + R_PAD) + 2 * R_FMAX * 32);
-    return (R_SMEM_LIMIT - 2048) / b32 >= 3 ? 32 : 16;
+// fixed shared memory beside the ring: the fits' coefficients, the list of non-zero column steps, slack
+static size_t round_fixed_smem(int ncs, int fmax) {
+    return sizeof(double) * (size_t)fmax * ncs + sizeof(int) * (size_t)(ncs / 4 + 4) + 2048;
 }
+static int round_rows_for(int ncs, int fmax) {
+    const size_t b32 = sizeof(double) * ((size_t)32 * (ncs + R_PAD) + 2 * (size_t)fmax * 32);
+    return (R_SMEM_LIMIT - round_fixed_smem(ncs, fmax)) / b32 >= 3 ? 32 : 16;
+}
+// fits one CTA serves: four where the helpers run on the DMMA pipe (rows up to 320 staged columns, any
+// step but a fit's first); one on first steps and for wider rows (FMA-pipe helpers)
+static int round_fmax(int ncs, int init) { return ((ncs + 63) / 64 <= 5 && !init) ? R_FMAX : 1; }
 
 int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std::vector<RoundProblem> &probs,
                      const std::vector<RoundFit> &fits, std::vector<RoundSlot> &slots, double **packed,
@@ -695,13 +830,14 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
     const int nfits = (int)fits.size(), P = (int)probs.size();
     if (ncs % 8 != 0 || ncs <= ni - 1 || iy >= ncs || ni < 1) return ate_fail(ctx, -1, "irls_round: bad staged width %d", ncs);
     const int it_e = (ncs + 63) / 64;
-    const int ROWS = round_rows_for(ncs);
-    const int fmax = it_e <= 5 ? R_FMAX : 1;  // the eval warps hold a beta slice per fit in registers
+    const int fmax = round_fmax(ncs, init);
+    // the slot geometry follows the widest variant (four fits) so that a fit's first step uses the same one
+    const int ROWS = round_rows_for(ncs, it_e <= 5 ? R_FMAX : 1);
     const size_t stage_bytes = sizeof(double) * ((size_t)ROWS * (ncs + R_PAD) + 2 * (size_t)fmax * ROWS);
-    int stages = (int)((R_SMEM_LIMIT - 2048) / stage_bytes);
+    int stages = (int)((R_SMEM_LIMIT - round_fixed_smem(ncs, fmax)) / stage_bytes);
     if (stages > R_MAX_STAGES) stages = R_MAX_STAGES;
     if (stages < 2 || it_e > 13) return ate_fail(ctx, -1, "irls_round: %d staged columns do not fit the step kernel", ncs);
-    const size_t smem = stages * stage_bytes + 3 * stages * sizeof(uint64_t);
+    const size_t smem = stages * stage_bytes + round_fixed_smem(ncs, fmax) - 1024;
     for (auto &pr : probs)
         if ((pr.ld & 1) != 0 || pr.ld < ncs) return ate_fail(ctx, -1, "irls_round: bad leading dimension");
 
@@ -783,7 +919,7 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
         gram_off[f] = part_doubles;
         part_doubles += (size_t)1024 * nblk * fit_chunks[f];
         eval_off[f] = part_doubles;
-        part_doubles += (size_t)eplen * fit_chunks[f];
+        part_doubles += ((size_t)eplen * fit_chunks[f] + 3) / 4 * 4;  // the next fit's tiles are stored 16 bytes at a time
     }
     void *dpacked = nullptr, *dpart = nullptr;
     ATE_TRY(ate_cached(ctx, "round.packed", sizeof(double) * (size_t)std::max(pk, 1LL), &dpacked));
@@ -861,12 +997,33 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
             }
     }
     st.ctas = nctas;
+    if (getenv("ATE_ROUND_DEBUG")) {  // the layout of a few rounds, for tuning the cost model
+        static int calls = 0;
+        if (calls < 4 || calls % 50 == 0) {
+            fprintf(stderr, "[ate round %d] %d live fits, %zu CTA kinds, %d CTAs, ROWS %d stages %d fmax %d init %d\n", calls, nlive,
+                    groups.size(), nctas, ROWS, stages, fmax, init);
+            for (size_t gi = 0; gi < groups.size() && gi < 12; ++gi) {
+                const Group &g = groups[gi];
+                int wmax = 0;
+                for (auto &b : g.bins) wmax = std::max(wmax, b.second.load);
+                fprintf(stderr, "   kind %zu: prob %d fits %d (nG %d, %d) lead %d bins %zu tiles %d busiest %d chunks %d rows/chunk %lld\n", gi,
+                        g.prob, g.nfit, fits[g.fit[0]].nG, g.nfit > 1 ? fits[g.fit[1]].nG : -1, g.lead[0], g.bins.size(), g.tiles, wmax,
+                        g.chunks, (long long)((probs[g.prob].nrows + g.chunks - 1) / g.chunks));
+            }
+        }
+        ++calls;
+    }
     ATE_CUDA(ctx, cudaMemcpyAsync(ddesc, hst, total, cudaMemcpyHostToDevice, ctx->stream));
     RArgs a;
     a.probs = (const DProb *)ddesc;
     a.fits = (const DFit *)((char *)ddesc + o_fits);
     a.ctas = (const DCta *)((char *)ddesc + o_ctas);
     a.ncols = ncs; a.ni = ni; a.iy = iy; a.stages = stages;
+    a.skip = ctx->debug_skip;
+    {
+        static const int hint = getenv("ATE_WAIT_HINT_NS") ? atoi(getenv("ATE_WAIT_HINT_NS")) : 0;
+        a.wait_hint = hint;
+    }
     const DFold *dfolds = (const DFold *)((char *)ddesc + o_folds);
 
     cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -877,18 +1034,19 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
     }
     int rc = -1;
     const bool in = init != 0;
-    if (ROWS == 32) {  // staged widths up to ~286 columns: at most five 64-column slices, two fits per CTA
-        if (it_e <= 1) rc = launch_round<32, 1, 2>(ctx, a, nctas, smem, in);
-        else if (it_e <= 2) rc = launch_round<32, 2, 2>(ctx, a, nctas, smem, in);
-        else if (it_e <= 3) rc = launch_round<32, 3, 2>(ctx, a, nctas, smem, in);
-        else if (it_e <= 4) rc = launch_round<32, 4, 2>(ctx, a, nctas, smem, in);
-        else rc = launch_round<32, 5, 2>(ctx, a, nctas, smem, in);
-    } else {
-        if (fmax == 2) rc = launch_round<16, 5, 2>(ctx, a, nctas, smem, in);
-        else if (it_e <= 7) rc = launch_round<16, 7, 1>(ctx, a, nctas, smem, in);
-        else if (it_e <= 9) rc = launch_round<16, 9, 1>(ctx, a, nctas, smem, in);
-        else rc = launch_round<16, 13, 1>(ctx, a, nctas, smem, in);
-    }
+    if (it_e <= 5) {  // rows up to 320 staged columns: four fits per CTA (one on a fit's first step)
+        if (ROWS == 32) {
+            if (it_e <= 1) rc = launch_narrow<32, 1>(ctx, a, nctas, smem, in);
+            else if (it_e <= 2) rc = launch_narrow<32, 2>(ctx, a, nctas, smem, in);
+            else if (it_e <= 3) rc = launch_narrow<32, 3>(ctx, a, nctas, smem, in);
+            else if (it_e <= 4) rc = launch_narrow<32, 4>(ctx, a, nctas, smem, in);
+            else rc = launch_narrow<32, 5>(ctx, a, nctas, smem, in);
+        } else {
+            rc = launch_narrow<16, 5>(ctx, a, nctas, smem, in);
+        }
+    } else if (it_e <= 7) rc = launch_round<16, 7, 1>(ctx, a, nctas, smem, in);
+    else if (it_e <= 9) rc = launch_round<16, 9, 1>(ctx, a, nctas, smem, in);
+    else rc = launch_round<16, 13, 1>(ctx, a, nctas, smem, in);
     if (rc < 0) return ate_fail(ctx, -1, "irls_round: cannot launch for %d staged columns", ncs);
     ATE_LAUNCHED(ctx);
     if (ctx->profile & 1) {
@@ -906,5 +1064,107 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
         ATE_LAUNCHED(ctx);
     }
     if (stats) *stats = st;
+    return 0;
+}
+
+// Measurement entry (include/ate_b200.h): `iters` launches of the step kernel on synthetic rows.
+extern "C" int ate_round_kernel_bench(ate_ctx *ctx, long long nrows, int ni, int nprob, int fits_per_prob, int list_cols,
+                                      int private_copy, int iters, int skip_mask, double *ms_per_launch, double *flops,
+                                      double *alg_bytes, int *ctas) {
+    if (!ctx) return -1;
+    if (nrows < 64 || ni < 1 || ni > 1024 || nprob < 1 || fits_per_prob < 1 || list_cols < 0 || list_cols > ni || iters < 1)
+        return ate_fail(ctx, -1, "ate_round_kernel_bench: bad arguments");
+    ATE_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int iy = ni, ncs = (ni + 1 + 7) / 8 * 8;
+    const long long ld = private_copy ? ncs + 4 : (ni + 3 + 31) / 32 * 32;
+    const int nfits = nprob * fits_per_prob, ldh = (ni + 31) / 32 * 32;
+    void *blk = nullptr;
+    const size_t xb = sizeof(double) * (size_t)nrows * (size_t)ld * nprob;
+    const size_t cb = sizeof(double) * (size_t)(ni + 1) * nfits, lb = sizeof(int) * (size_t)ldh * nfits;
+    ATE_TRY(ate_cached(ctx, "roundbench.state", xb + cb + lb + 1024, &blk));
+    double *dX = (double *)blk;
+    double *dcoef = (double *)((char *)blk + xb);
+    int *dlist = (int *)((char *)blk + xb + cb);
+    {   // rows: small deterministic values, response column 0/1, pad zero
+        std::vector<double> row((size_t)ld * 4096);
+        for (long long r0 = 0; r0 < nrows * nprob; r0 += 4096) {
+            const long long cnt = std::min<long long>(4096, nrows * nprob - r0);
+            for (long long r = 0; r < cnt; ++r)
+                for (long long c = 0; c < ld; ++c) {
+                    const unsigned h = (unsigned)((r0 + r) * 2654435761u + c * 40503u);
+                    row[r * ld + c] = c < ni ? ((h >> 8) & 1023) / 512.0 - 1.0 : (c == iy ? (double)((h >> 5) & 1) : (c == ni + 2 && !private_copy ? 1.0 : 0.0));
+                }
+            ATE_CUDA(ctx, cudaMemcpyAsync(dX + (size_t)r0 * ld, row.data(), sizeof(double) * (size_t)cnt * ld, cudaMemcpyHostToDevice, ctx->stream));
+            ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        }
+        std::vector<double> hc((size_t)(ni + 1) * nfits, 0.0);
+        std::vector<int> hl((size_t)ldh * nfits, ncs);
+        for (int f = 0; f < nfits; ++f) {
+            for (int j = 0; j < list_cols; ++j) {
+                hl[(size_t)f * ldh + j] = (j * 7 + f) % ni;  // scattered columns, as a strong set is
+                hc[(size_t)f * (ni + 1) + hl[(size_t)f * ldh + j]] = 0.01 * ((j % 5) - 2);
+            }
+            hc[(size_t)f * (ni + 1) + ni] = -0.3;
+        }
+        ATE_CUDA(ctx, cudaMemcpyAsync(dcoef, hc.data(), cb, cudaMemcpyHostToDevice, ctx->stream));
+        ATE_CUDA(ctx, cudaMemcpyAsync(dlist, hl.data(), lb, cudaMemcpyHostToDevice, ctx->stream));
+        ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    std::vector<RoundProblem> probs(nprob);
+    std::vector<RoundFit> fits(nfits);
+    for (int p = 0; p < nprob; ++p) probs[p] = RoundProblem{dX + (size_t)p * nrows * ld, ld, nullptr, nrows};
+    for (int f = 0; f < nfits; ++f) {
+        RoundFit &r = fits[f];
+        r.prob = f / fits_per_prob;
+        const int k = f % fits_per_prob;
+        r.hole_begin = fits_per_prob > 1 ? nrows / fits_per_prob * k : 0;
+        r.hole_len = fits_per_prob > 1 ? nrows / fits_per_prob : 0;
+        r.w = 1.0 / (double)nrows;
+        r.coef = dcoef + (size_t)f * (ni + 1);
+        r.colidx = dlist + (size_t)f * ldh;
+        r.nG = list_cols;
+        r.live = 1;
+    }
+    std::vector<RoundSlot> slots;
+    double *packed = nullptr;
+    long long count = 0;
+    RoundStats st;
+    ctx->debug_skip = skip_mask;
+    int rc = ate_i_irls_round(ctx, ncs, ni, iy, 0, probs, fits, slots, &packed, &count, &st);  // warm-up
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    float ms = 0.f;
+    if (rc == 0 && cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess) {
+        cudaStreamSynchronize(ctx->stream);
+        cudaEventRecord(e0, ctx->stream);
+        for (int it = 0; it < iters && rc == 0; ++it) rc = ate_i_irls_round(ctx, ncs, ni, iy, 0, probs, fits, slots, &packed, &count, &st);
+        cudaEventRecord(e1, ctx->stream);
+        if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = ate_fail(ctx, -100, "ate_round_kernel_bench: %s", cudaGetErrorString(cudaGetLastError()));
+        cudaEventElapsedTime(&ms, e0, e1);
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    ctx->debug_skip = 0;
+#ifdef ATE_ROUND_TRACE
+    if (const char *path = getenv("ATE_ROUND_TRACE_OUT")) {
+        static long long hbuf[TR_SLOTS * TR_EVENTS + 8];
+        if (cudaMemcpyFromSymbol(hbuf, g_rtrace, sizeof(hbuf)) == cudaSuccess) {
+            if (FILE *f = fopen(path, "w")) {
+                fprintf(f, "slot,prod_free,e0_start,e1_start,e0_pub,e1_pub,h0_start,h1_start,h0_done,h1_done,m0_start,m0_done,m1_start,m1_done,m2_start,m2_done\n");
+                long long base = hbuf[8];
+                for (int it = 0; it < TR_SLOTS; ++it) {
+                    fprintf(f, "%d", it);
+                    for (int e = 0; e < 15; ++e) fprintf(f, ",%lld", hbuf[8 + it * TR_EVENTS + e] ? hbuf[8 + it * TR_EVENTS + e] - base : -1);
+                    fprintf(f, "\n");
+                }
+                fclose(f);
+            }
+        }
+    }
+#endif
+    if (rc < 0) return rc;
+    if (ms_per_launch) *ms_per_launch = ms / iters;
+    if (flops) *flops = st.flops;
+    if (alg_bytes) *alg_bytes = st.alg_bytes;
+    if (ctas) *ctas = st.ctas;
     return 0;
 }

@@ -172,6 +172,27 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def per_row_scaling(n_sample, n_full):
+    """seconds-per-row of the CPU port's nuisance fits at n_full relative to n_sample, from the one-machine
+    measurements in profiles/r02_cpu_linearity.jsonl (tools/cpu_linearity.py: n = 10k .. 1M at a fixed thread
+    count).  glmnet needs fewer passes per row as n grows, so a small sample scaled linearly would OVERSTATE
+    the CPU time of the full workload (by 2.0x from n = 10k); this factor takes that out.  1.0 when the
+    file is missing or the sizes fall outside what was measured."""
+    try:
+        pts = sorted((json.loads(l)["n"], json.loads(l)["fit_s_per_row"])
+                     for l in open(os.path.join(ROOT, "profiles", "r02_cpu_linearity.jsonl")) if l.strip())
+    except Exception:
+        return 1.0, "no linearity file: scaled linearly in n"
+    if len(pts) < 2:
+        return 1.0, "no linearity file: scaled linearly in n"
+    xs = np.log([p[0] for p in pts])
+    ys = np.log([p[1] for p in pts])
+    at = lambda n: float(np.exp(np.interp(np.log(n), xs, ys)))
+    f = at(n_full) / at(n_sample)
+    return f, (f"seconds per row at n={n_full} are {f:.3f} x those at n={n_sample} on one machine "
+               "(profiles/r02_cpu_linearity.jsonl)")
+
+
 def cpu_sample(args, n_sample, threads):
     """One fit of the CPU oracle on a bounded sample of the same workload (same p, K, inner folds and
     lambdas; n_sample rows; Bs replicates), on exactly `threads` OpenMP threads.  The two legs scale
@@ -194,17 +215,18 @@ def cpu_sample(args, n_sample, threads):
         t = time.perf_counter()
         O.bootstrap_idx(d["w"], d["y"], r["phat"], r["m0"], r["m1"], bidx)
         t_boot = time.perf_counter() - t
-    full_s = t_fit * (args.n / n_sample) + (t_boot * (args.B * args.n) / (Bs * n_sample) if Bs > 0 else 0.0)
+    corr, corr_text = per_row_scaling(n_sample, args.n)
+    full_s = t_fit * (args.n / n_sample) * corr + (t_boot * (args.B * args.n) / (Bs * n_sample) if Bs > 0 else 0.0)
     return dict(n=n_sample, B=Bs, threads=used, fit_s=t_fit, boot_s=t_boot, sample_s=t_fit + t_boot,
-                full_workload_s=full_s, fits_per_s=1.0 / full_s)
+                full_workload_s=full_s, fits_per_s=1.0 / full_s, per_row_scaling=corr, per_row_scaling_text=corr_text)
 
 
 def sample_text(args, s):
     return (f"one full fit of the CPU port at n={s['n']} (same p={design_width(args.p0, args.expand)}, K=5, 10 inner "
             f"folds, {args.nlambda} lambdas) took {s['fit_s']:.2f} s and B={s['B']} index-mode replicates {s['boot_s']:.2f} s "
-            f"on {s['threads']} threads; extrapolated to n={args.n}, B={args.B}: nuisance fits x{args.n / s['n']:.0f} (linear "
-            f"in n), bootstrap x{(args.B * args.n) / max(1, s['B'] * s['n']):.0f} (linear in B*n) = {s['full_workload_s']:.0f} s "
-            "per fit.  R and glmnet are not installed on this box: the timed code is oracle/ate_oracle.c, a C "
+            f"on {s['threads']} threads; extrapolated to n={args.n}, B={args.B}: nuisance fits x{args.n / s['n']:.0f} x "
+            f"{s['per_row_scaling']:.3f} ({s['per_row_scaling_text']}), bootstrap x{(args.B * args.n) / max(1, s['B'] * s['n']):.0f} "
+            f"(linear in B*n) = {s['full_workload_s']:.0f} s per fit.  R and glmnet are not installed on this box: the timed code is oracle/ate_oracle.c, a C "
             "restatement of glmnet's coordinate descent, cv.glmnet and the reference's bootstrap loop")
 
 

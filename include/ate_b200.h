@@ -307,13 +307,25 @@ ATE_API int ate_cv_select(int nfolds, int lmu, const double *cvraw, const double
  * lists hold list_cols[f] columns (the strong set plus candidates), on a design that stages
  * `staged_cols` columns per row, returns how the step kernel groups them into CTAs: the return value is
  * the number of CTA kinds G (<= max_groups, else -2), and desc[24 g + ...] describes kind g:
- *   [0] fits served (1 or 2), [1], [2] their indices, [3], [4] whether this kind evaluates the fit's
- *   sums (a list too wide for one CTA is split over several kinds; the first one leads),
+ *   [0] fits served (1 to 4), [1 .. 4] their indices, [5] bit s set when this kind evaluates the sums
+ *   of its fit s (a list too wide for one CTA is split over several kinds; the first one leads),
  *   [8 + 2 w], [9 + 2 w] for MMA warp w = 0..7: x = fit slot | segment << 8 | count << 16, y = up to four
  *   tile-row numbers, one per byte (count 0: the warp idles).
  * Lets tests check on a CPU-only box that every 8x8 tile of every fit's lower triangle is computed
  * exactly once for every mix of widths.  -1 for widths the step cannot take. */
 ATE_API int ate_round_plan_describe(int nfit, const int *list_cols, int staged_cols, int max_groups, unsigned *desc);
+
+/* ---- the step kernel alone, on synthetic rows (measurement; no counterpart in the reference) ----- */
+/* Times `iters` launches of irls_round_kernel (with its fold kernels) on nprob synthetic problems of
+ * nrows rows x ni columns, each with fits_per_prob path fits whose Gram lists hold list_cols scattered
+ * columns (fits_per_prob > 1: every fit gives its own 1/fits_per_prob of the rows weight 0, as the
+ * cv-fold fits do).  private_copy != 0: the contiguous row layout the binomial driver stages from.
+ * skip_mask idles roles of the kernel (1 MMA, 2 helpers, 4 eval's exp / log, 8 eval's dot) to see what
+ * paces it; results are then meaningless.  Outputs: ms per launch (CUDA events on the ctx stream), the
+ * algorithmic flop and bytes of one launch and the CTAs launched.  tools/round_bench.py. */
+ATE_API int ate_round_kernel_bench(ate_ctx *ctx, long long nrows, int ni, int nprob, int fits_per_prob, int list_cols,
+                           int private_copy, int iters, int skip_mask, double *ms_per_launch, double *flops,
+                           double *alg_bytes, int *ctas);
 
 #ifdef __cplusplus
 }

@@ -155,7 +155,7 @@ def test_gloo_exchange_between_ranks(tmp_path, world):
 
 def _check_round_plan(lib, widths, staged):
     """Every 8x8 tile of every fit's lower triangle is owned by exactly one MMA warp of one CTA kind; a CTA
-    kind serves at most two fits and each fit is evaluated (led) by exactly one kind."""
+    kind serves at most four fits and each fit is evaluated (led) by exactly one kind."""
     widths = np.asarray(widths, dtype=np.int32)
     desc = (C.c_uint * (24 * 128))()
     ng = lib.ate_round_plan_describe(len(widths), widths.ctypes.data_as(C.c_void_p), staged, 128, desc)
@@ -165,10 +165,10 @@ def _check_round_plan(lib, widths, staged):
     for g in range(ng):
         d = desc[24 * g: 24 * g + 24]
         nfit = d[0]
-        assert 1 <= nfit <= 2
+        assert 1 <= nfit <= 4
         fits = [d[1 + s] for s in range(nfit)]
         for s in range(nfit):
-            if d[3 + s]:
+            if (d[5] >> s) & 1:
                 leads[fits[s]] = leads.get(fits[s], 0) + 1
         for w in range(8):
             x, y = d[8 + 2 * w], d[9 + 2 * w]
@@ -202,7 +202,8 @@ def test_step_kernel_work_plan_covers_every_tile_once():
     lib = _lib.load()
     for cols in list(range(0, 130)) + [160, 200, 255, 256, 300, 412, 513, 1024]:
         _check_round_plan(lib, [cols], 264)
-    assert _check_round_plan(lib, [64] * 10, 264) == 5           # two fits per CTA at the C1 width
+    assert _check_round_plan(lib, [64] * 10, 264) == 5           # 36 tiles per fit: two fits fill a CTA's eight MMA warps
+    assert _check_round_plan(lib, [32] * 10, 264) == 3           # 10 tiles per fit: four fits per CTA
     assert _check_round_plan(lib, [64] * 10, 520) == 10          # wide rows (C4): one fit per CTA
     assert _check_round_plan(lib, [200], 264) >= 2                # a list too wide for one CTA is split
     rng = np.random.default_rng(3)

@@ -15,7 +15,7 @@ for what in "$@"; do
 case $what in
 probe)
     step probe_round 300 python tools/gpu_probe_round.py ;;
-sanitize)
+sanitize_closed)
     PROBE_ONLY="n200" step sanitize_memcheck 600 compute-sanitizer --tool memcheck --print-limit 20 python tools/gpu_probe_round.py ;;
 kernels)
     step t_kernels 600 python -m pytest tests/test_gpu_kernels.py -x -q ;;
@@ -27,13 +27,24 @@ tests)
     step t_round2 900 python -m pytest tests/test_gpu_round2.py tests/test_zz_no_alloc.py -x -q ;;
 alltests)
     step t_all 1500 python -m pytest tests -m gpu -x -q ;;
+rbench)
+    step round_bench 600 python tools/round_bench.py --cases 1x1,5x1,5x10 --lists 0,32,48,64,96 --skips 0,1,2,15 ;;
+ncu_rb)
+    step ncu_rb 600 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 2 -c 1 -o gpurun_out/ncu_rb python tools/round_bench.py --cases 5x10 --lists 32 --skips 0 --iters 3
+    ncu -i gpurun_out/ncu_rb.ncu-rep --page source --csv > gpurun_out/ncu_rb_source.csv 2>/dev/null
+    ncu -i gpurun_out/ncu_rb.ncu-rep --page raw --csv > gpurun_out/ncu_rb_raw.csv 2>/dev/null ;;
+trace)
+    for c in "1x1 64" "5x10 32" "5x10 64"; do set -- $c; tag=$(echo $1_$2)
+      ATE_B200_LIB=$PWD/ate_replication_causalml_b200/libate_b200_trace.so ATE_ROUND_TRACE_OUT=gpurun_out/trace_$tag.csv step trace_$tag 300 python tools/round_bench.py --cases $1 --lists $2 --skips 0 --iters 2
+      python tools/round_trace.py gpurun_out/trace_$tag.csv 60 76
+    done ;;
 smoke)
     step smoke 300 python -c "import __graft_entry__ as g; g.smoke()" ;;
 bench)
     ATE_TIMING=1 step bench_c1 900 python bench.py --steps 2 --warmup 2
     grep -h '^{' gpurun_out/bench_c1.log | tail -1 > gpurun_out/bench_c1.json ;;
 benchq)
-    step bench_c1q 600 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e
+    ATE_PROFILE_CSV=gpurun_out/round_launches.csv ATE_ROUND_DEBUG=1 step bench_c1q 600 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e
     grep -h '^{' gpurun_out/bench_c1q.log | tail -1 > gpurun_out/bench_c1q.json ;;
 ref)
     step bench_ref 600 python bench.py --impl reference --steps 1 --warmup 1 --linearity
