@@ -69,7 +69,7 @@ struct DCta {
     int prob, nfit, chunk, pad;
     long long row_begin, row_end;
     int fit[R_FMAX], lead[R_FMAX];
-    uint2 mma[R_CWARPS];  // x = fit slot | segment << 8 | count << 16, y = four tile-row numbers (bytes)
+    uint2 mma[R_CWARPS];  // per MMA warp two halves (x, y): fit slot | segment << 2 | count << 8 | row0 << 10 | row1 << 18
 };
 struct DFold {
     const double *gram_part, *eval_part;
@@ -81,6 +81,7 @@ struct RArgs {
     const DFit *fits;
     const DCta *ctas;
     int ncols, ni, iy, stages;
+    int rolemap;    // 1: warps of a sub-partition share a role (see the kernel)
     int wait_hint;  // ns of suspend-time hint for the barrier waits (0: plain try_wait)
     int skip;  // measurement only (ate_round_kernel_bench): 1 MMA idle, 2 helpers idle, 4 eval without exp/log, 8 eval without dot
 };
@@ -125,16 +126,6 @@ __device__ __forceinline__ void wait_g(uint64_t *bar, uint32_t parity, uint32_t 
     }
 }
 
-// C(8x8) += A(8x4) * B(4x8) when `on` (a warp-uniform flag) is set.  The predicate sits on the MMA
-// itself, so the instruction stream has no branch around it (and no re-convergence barrier per tile).
-__device__ __forceinline__ void dmma884_if(int on, double &c0, double &c1, double a, double b) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.s32 p, %4, 0;\n\t"
-        "@p mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n\t}"
-        : "+d"(c0), "+d"(c1)
-        : "d"(a), "d"(b), "r"(on));
-}
 
 // -DATE_ROUND_TRACE: CTA 0 stamps clock64() per slot and role into a device buffer which
 // ate_round_kernel_bench writes to $ATE_ROUND_TRACE_OUT (tools/round_trace.py prints the timeline).
@@ -172,7 +163,11 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
     uint64_t *full = reinterpret_cast<uint64_t *>(skk + ((ncols / 4 + 3) & ~1));
     uint64_t *vfull = full + stages, *empty = vfull + stages;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // Hardware warp w runs on SM sub-partition w % 4.  With rolemap the roles are dealt so that the warps
+    // of a sub-partition run the SAME loop (MMA on sub-partitions 0-1, producer + helpers on 2, eval on
+    // 3): the sub-partition's instruction cache then holds one hot loop instead of three.
+    const int hw_warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = a.rolemap ? (((hw_warp & 3) << 2) | (hw_warp >> 2)) : hw_warp;
     const uint32_t whint = (uint32_t)a.wait_hint;
     if (threadIdx.x < (int)(sizeof(DCta) / sizeof(int)))
         reinterpret_cast<int *>(&scta)[threadIdx.x] = reinterpret_cast<const int *>(a.ctas + blockIdx.x)[threadIdx.x];
@@ -333,13 +328,23 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             const double *arow = slot + (size_t)rr * pitch + k4;
             double c0 = 0.0, c1 = 0.0, d0 = 0.0, d1 = 0.0;  // two accumulation chains
             int j = 0;
-#pragma unroll 2
-            for (; j + 1 < nk; j += 2) {
-                const int ka = skk[j] << 2, kb = skk[j + 1] << 2;
-                dmma884(c0, c1, arow[ka], bok ? brow[ka] : 0.0);
-                dmma884(d0, d1, arow[kb], bok ? brow[kb] : 0.0);
+            for (; j + 7 < nk; j += 8) {  // eight steps at a time: their operand loads overlap
+                int kq[8];
+                double aq[8], bq[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) kq[u] = skk[j + u] << 2;
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    aq[u] = arow[kq[u]];
+                    bq[u] = bok ? brow[kq[u]] : 0.0;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; u += 2) {
+                    dmma884(c0, c1, aq[u], bq[u]);
+                    dmma884(d0, d1, aq[u + 1], bq[u + 1]);
+                }
             }
-            if (j < nk) {
+            for (; j < nk; ++j) {
                 const int ka = skk[j] << 2;
                 dmma884(c0, c1, arow[ka], bok ? brow[ka] : 0.0);
             }
@@ -411,21 +416,25 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         bool any_lead = false;
 #pragma unroll
         for (int f = 0; f < FMAX; ++f) any_lead |= (f < nfit && scta.lead[f] != 0);
-        if constexpr (HDMMA) {
+        if (HDMMA && nfit > 1) {
             // [r_0 v_0 r_1 v_1 ...]^T X on the DMMA pipe: the eight rows of A are (fit, r | v) pairs, a tile
             // of B is four staged rows x eight CONSECUTIVE columns (conflict-free loads), so one DMMA per
             // tile and k-step serves X^T r and X^T v of up to four fits.  The column tiles are split
             // between the helper warps (three when one producer suffices, else two).
-            const int ntile = ncols >> 3, tpw = (ntile + nhelp - 1) / nhelp;
-            const int tile0 = h * tpw;
-            int nmy = ntile - tile0;
-            nmy = nmy < 0 ? 0 : (nmy > tpw ? tpw : nmy);
+            // Every helper takes the same number of tiles, a compile-time constant per helper count, and
+            // issues them WITHOUT a guard: a guarded mma.sync costs a re-convergence barrier per instruction
+            // (measured: ~25 cycles each, more than the DMMA itself).  Tiles past the last column read
+            // whatever follows the row (finite staged data) and their sums are never written out.
+            const int ntile = ncols >> 3;
             const int g = lane >> 2, k4 = lane & 3;
             const int af = g >> 1;               // the fit whose r (g even) or v (g odd) this lane feeds into A
             const bool a_ok = af < nfit && af < FMAX;
             double acc[HT][2];
 #pragma unroll
             for (int t = 0; t < HT; ++t) acc[t][0] = acc[t][1] = 0.0;
+            constexpr int HT3 = (ITER * 8 + 2) / 3;   // tiles per helper when there are three
+            const int tpw = nhelp == 3 ? HT3 : HT;
+            const int tile0 = h * tpw;
             for (int it = 0; it < nit; ++it) {
                 const int s = it % stages;
                 const uint32_t ph = (uint32_t)(it / stages) & 1u;
@@ -435,14 +444,24 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
                     if (h < 2) RTRACE(5 + h, it);  // helper h: start
                     const double *slot = sx + stage_doubles * s;
                     const double *srcA = ((g & 1) ? sv : sr) + ((size_t)s * FMAX + (a_ok ? af : 0)) * ROWS;
+                    if (nhelp == 3) {
 #pragma unroll 1
-                    for (int kk = 0; kk < ROWS / 4; ++kk) {
-                        const int r = kk * 4 + k4;
-                        const double av = a_ok ? srcA[r] : 0.0;
-                        const double *rowp = slot + (size_t)r * pitch + tile0 * 8 + g;
+                        for (int kk = 0; kk < ROWS / 4; ++kk) {
+                            const int r = kk * 4 + k4;
+                            const double av = a_ok ? srcA[r] : 0.0;
+                            const double *rowp = slot + (size_t)r * pitch + tile0 * 8 + g;
 #pragma unroll
-                        for (int t = 0; t < HT; ++t)
-                            if (t < nmy) dmma884(acc[t][0], acc[t][1], av, rowp[t * 8]);
+                            for (int t = 0; t < HT3; ++t) dmma884(acc[t][0], acc[t][1], av, rowp[t * 8]);
+                        }
+                    } else {
+#pragma unroll 1
+                        for (int kk = 0; kk < ROWS / 4; ++kk) {
+                            const int r = kk * 4 + k4;
+                            const double av = a_ok ? srcA[r] : 0.0;
+                            const double *rowp = slot + (size_t)r * pitch + tile0 * 8 + g;
+#pragma unroll
+                            for (int t = 0; t < HT; ++t) dmma884(acc[t][0], acc[t][1], av, rowp[t * 8]);
+                        }
                     }
                 }
                 __syncwarp();
@@ -454,16 +473,17 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
                 double *ep = a.fits[scta.fit[af]].eval_part + (size_t)scta.chunk * (3 * ni + 3 * R_EWARPS) + ((g & 1) ? ni : 0);
 #pragma unroll
                 for (int t = 0; t < HT; ++t)
-                    if (t < nmy) {
+                    if (t < tpw && tile0 + t < ntile) {
                         const int c = (tile0 + t) * 8 + 2 * k4;
                         if (c < ni) ep[c] = acc[t][0];
                         if (c + 1 < ni) ep[c + 1] = acc[t][1];
                     }
             }
         } else {
-            // FMA-pipe form (first step of a fit, and rows wider than 320 columns; one fit per CTA there):
-            // lanes own column pairs, the columns are split between the helper warps
-            static_assert(HDMMA || FMAX == 1, "the FMA-pipe helper serves one fit");
+            // FMA-pipe form, for a CTA that serves ONE fit (first step of a fit, rows wider than 320 columns,
+            // lists too wide to share a CTA): an 8-row MMA tile would carry two useful rows, so the plain
+            // FMA pipe is cheaper here and leaves the DMMA pipe to the Gram.  Lanes own column pairs, the
+            // columns are split between the helper warps.
             const int npairs = ncols >> 1, ppw = (npairs + nhelp - 1) / nhelp;
             double gr[2 * ITERH], hx[2 * ITERH], hxx[INIT ? 2 * ITERH : 1];
 #pragma unroll
@@ -523,19 +543,31 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         }
     } else if (warp < R_CWARPS) {
         // ------------------------------ MMA ------------------------------
+        // two halves per warp; a half = up to two tile rows of one 32-column segment of one fit
         const uint2 d = scta.mma[warp];
-        const int fs = (int)(d.x & 0xffu), seg = (int)((d.x >> 8) & 0xffu), cnt = (int)((d.x >> 16) & 0xffu);
         const int g = lane >> 2, k4 = lane & 3;
-        int nt[4], offA[4], offB[4], tr[4];
-        const int *colidx = cnt > 0 ? a.fits[scta.fit[fs]].colidx : nullptr;
+        int fsl[2], seg[2], nt[4], tr[4], offA[4], offB[2][4];
+        bool any = false;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            tr[u] = (int)((d.y >> (8 * u)) & 0xffu);
-            const int lim = tr[u] - 4 * seg + 1;  // tiles left of (and on) the diagonal in this segment
-            nt[u] = u < cnt ? (lim < 4 ? lim : 4) : 0;
-            offA[u] = nt[u] > 0 ? __ldg(colidx + tr[u] * 8 + g) : 0;
-            offB[u] = cnt > 0 ? __ldg(colidx + (4 * seg + u) * 8 + g) : 0;
+        for (int hh = 0; hh < 2; ++hh) {
+            const unsigned wd = hh ? d.y : d.x;
+            fsl[hh] = (int)(wd & 3u);
+            seg[hh] = (int)((wd >> 2) & 63u);
+            const int cnt = (int)((wd >> 8) & 3u);
+            const int *colidx = cnt > 0 ? a.fits[scta.fit[fsl[hh]]].colidx : nullptr;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int u = 2 * hh + j;
+                tr[u] = (int)((wd >> (10 + 8 * j)) & 255u);
+                const int lim = tr[u] - 4 * seg[hh] + 1;  // tiles left of (and on) the diagonal in this segment
+                nt[u] = j < cnt ? (lim < 4 ? lim : 4) : 0;
+                offA[u] = nt[u] > 0 ? __ldg(colidx + tr[u] * 8 + g) : 0;
+            }
+#pragma unroll
+            for (int n = 0; n < 4; ++n) offB[hh][n] = cnt > 0 ? __ldg(colidx + (4 * seg[hh] + n) * 8 + g) : 0;
+            any |= cnt > 0;
         }
+        const bool same = (fsl[0] == fsl[1] && seg[0] == seg[1]);  // both halves read the same B operands
         double acc[4][4][2];
 #pragma unroll
         for (int u = 0; u < 4; ++u)
@@ -545,32 +577,43 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
             wait_g(full + s, ph, whint);
-            if (cnt > 0 && !(a.skip & 1)) {
+            if (any && !(a.skip & 1)) {
                 wait_g(vfull + s, ph, whint);
                 if (warp < 3) RTRACE(9 + 2 * warp, it);  // MMA warp 0..2: start
                 const double *base = sx + stage_doubles * s;
-                const double *vs = sv + ((size_t)s * FMAX + fs) * ROWS;
+                const double *vs0 = sv + ((size_t)s * FMAX + fsl[0]) * ROWS, *vs1 = sv + ((size_t)s * FMAX + fsl[1]) * ROWS;
 #pragma unroll 1
                 for (int kk = 0; kk < ROWS / 4; ++kk) {
                     const int r = kk * 4 + k4;
                     const double *rowp = base + (size_t)r * pitch;
-                    const double vv = vs[r];
                     double fb[4];
 #pragma unroll
-                    for (int n = 0; n < 4; ++n) fb[n] = rowp[offB[n]] * vv;
-                    // nt[u] is the same in every lane: the branches below are uniform, and only the tiles
-                    // the warp owns cost an instruction
+                    for (int hh = 0; hh < 2; ++hh) {
+                        if (hh == 0 || !same) {  // (warp-uniform)
+                            const double vv = hh ? vs1[r] : vs0[r];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        if (nt[u] > 0) {
+                            for (int n = 0; n < 4; ++n) fb[n] = rowp[offB[hh][n]] * vv;
+                        }
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            // one (warp-uniform) branch per tile row, then straight-line MMAs: a guard on every
+                            // mma.sync would cost a re-convergence barrier per instruction
+                            const int u = 2 * hh + j;
                             const double fa = rowp[offA[u]];
-                            dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
-                            if (nt[u] > 1) {
+                            if (nt[u] == 4) {
+                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
                                 dmma884(acc[u][1][0], acc[u][1][1], fa, fb[1]);
-                                if (nt[u] > 2) {
-                                    dmma884(acc[u][2][0], acc[u][2][1], fa, fb[2]);
-                                    if (nt[u] > 3) dmma884(acc[u][3][0], acc[u][3][1], fa, fb[3]);
-                                }
+                                dmma884(acc[u][2][0], acc[u][2][1], fa, fb[2]);
+                                dmma884(acc[u][3][0], acc[u][3][1], fa, fb[3]);
+                            } else if (nt[u] == 3) {
+                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
+                                dmma884(acc[u][1][0], acc[u][1][1], fa, fb[1]);
+                                dmma884(acc[u][2][0], acc[u][2][1], fa, fb[2]);
+                            } else if (nt[u] == 2) {
+                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
+                                dmma884(acc[u][1][0], acc[u][1][1], fa, fb[1]);
+                            } else if (nt[u] == 1) {
+                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
                             }
                         }
                     }
@@ -581,20 +624,18 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             if (lane == 0) mbar_arrive(empty + s);
         }
         // tile (tr[u], 4 seg + n) sits in 32x32 block (tr[u] / 4, seg) of the fold kernel's layout
-        if (cnt > 0) {
-            const DFit &ft = a.fits[scta.fit[fs]];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (nt[u] > 0) {
-                    const int bi = tr[u] >> 2, m = tr[u] & 3;
-                    double *out = ft.gram_part + ((size_t)scta.chunk * ft.nblk + (bi * (bi + 1) / 2 + seg)) * 1024;
+        for (int u = 0; u < 4; ++u) {
+            if (nt[u] > 0) {
+                const DFit &ft = a.fits[scta.fit[fsl[u >> 1]]];
+                const int bi = tr[u] >> 2, m = tr[u] & 3;
+                double *out = ft.gram_part + ((size_t)scta.chunk * ft.nblk + (bi * (bi + 1) / 2 + seg[u >> 1])) * 1024;
 #pragma unroll
-                    for (int n = 0; n < 4; ++n)
-                        if (n < nt[u]) {
-                            const int r = m * 8 + g, c = n * 8 + 2 * k4;
-                            *reinterpret_cast<double2 *>(out + r * 32 + c) = make_double2(acc[u][n][0], acc[u][n][1]);
-                        }
-                }
+                for (int n = 0; n < 4; ++n)
+                    if (n < nt[u]) {
+                        const int r = m * 8 + g, c = n * 8 + 2 * k4;
+                        *reinterpret_cast<double2 *>(out + r * 32 + c) = make_double2(acc[u][n][0], acc[u][n][1]);
+                    }
             }
         }
     }
@@ -641,30 +682,35 @@ round_fold_gram_kernel(const DFold *__restrict__ folds) {
     fd.H[e] = s;
 }
 
-// ---- host: tile-row bins ---------------------------------------------------------------------
+// ---- host: who computes which Gram tiles ----------------------------------------------------------
 // For a list of ntr = ceil(nG / 8) tile rows: segment sg (columns 32 sg .. 32 sg + 31 of the list)
-// holds tile rows r >= 4 sg with min(4, r - 4 sg + 1) tiles each.  A bin is what one MMA warp takes:
-// <= 4 tile rows of ONE segment (they share the four B operands), packed first-fit-decreasing under
-// a load bound T.
-struct Bin {
-    int seg, cnt, load, rows[4];
+// holds tile rows r >= 4 sg with min(4, r - 4 sg + 1) tiles each.  The unit of work is a HALF: one or two
+// tile rows of ONE segment of ONE fit (they share the four B operands), at most eight tiles.  An MMA warp
+// owns two halves (16 tiles, 64 accumulator registers), which may belong to different fits: narrow lists
+// of several fits then fill a CTA's eight warps, and the staged rows serve up to four fits.
+struct Half {
+    int fit, seg, cnt, load, rows[2];
 };
-void pack_bins(int ntr, int T, std::vector<Bin> &out) {
-    out.clear();
+// halves of one fit: within a segment the rows are paired heaviest with lightest
+void make_halves(int fit, int ntr, std::vector<Half> &out) {
     const int nseg = (ntr + 3) / 4;
     for (int sg = 0; sg < nseg; ++sg) {
-        const size_t first = out.size();
-        std::vector<int> order;
-        for (int r = 4 * sg + 3; r < ntr; ++r) order.push_back(r);
-        for (int r = (4 * sg + 2 < ntr - 1 ? 4 * sg + 2 : ntr - 1); r >= 4 * sg; --r) order.push_back(r);
-        for (int r : order) {
-            const int c = r - 4 * sg + 1 < 4 ? r - 4 * sg + 1 : 4;
-            size_t k = first;
-            for (; k < out.size(); ++k)
-                if (out[k].cnt < 4 && out[k].load + c <= T) break;
-            if (k == out.size()) out.push_back(Bin{sg, 0, 0, {0, 0, 0, 0}});
-            out[k].rows[out[k].cnt++] = r;
-            out[k].load += c;
+        std::vector<int> rows;
+        for (int r = 4 * sg; r < ntr; ++r) rows.push_back(r);
+        auto tiles = [&](int r) { return r - 4 * sg + 1 < 4 ? r - 4 * sg + 1 : 4; };
+        std::stable_sort(rows.begin(), rows.end(), [&](int x, int y) { return tiles(x) > tiles(y); });
+        size_t lo = 0, hi = rows.size();
+        while (lo < hi) {
+            Half h{fit, sg, 0, 0, {0, 0}};
+            h.rows[h.cnt++] = rows[lo];
+            h.load += tiles(rows[lo]);
+            ++lo;
+            if (lo < hi) {
+                --hi;
+                h.rows[h.cnt++] = rows[hi];
+                h.load += tiles(rows[hi]);
+            }
+            out.push_back(h);
         }
     }
 }
@@ -672,22 +718,46 @@ void pack_bins(int ntr, int T, std::vector<Bin> &out) {
 struct Group {
     int prob = 0;
     int nfit = 0, fit[R_FMAX] = {0, 0, 0, 0}, lead[R_FMAX] = {0, 0, 0, 0};
-    std::vector<std::pair<int, Bin>> bins;  // (fit slot, bin), <= R_CWARPS
+    std::vector<Half> halves;   // .fit = fit SLOT; <= 2 R_CWARPS, dealt to the warps by deal_halves
+    Half warp_half[R_CWARPS][2];
     int tiles = 0;
     double cost = 0.0;
     int chunks = 1;
 };
 
+// two halves per warp: heaviest first onto the lightest warp that has room, preferring a warp that
+// already holds a half of the same fit and segment (its B operands are then loaded once)
+void deal_halves(Group &g) {
+    for (int w = 0; w < R_CWARPS; ++w) g.warp_half[w][0] = g.warp_half[w][1] = Half{0, 0, 0, 0, {0, 0}};
+    std::vector<Half> hs = g.halves;
+    std::stable_sort(hs.begin(), hs.end(), [](const Half &x, const Half &y) { return x.load > y.load; });
+    int cnt[R_CWARPS] = {0}, load[R_CWARPS] = {0};
+    for (const Half &h : hs) {
+        int best = -1;
+        for (int w = 0; w < R_CWARPS; ++w) {
+            if (cnt[w] >= 2) continue;
+            if (best < 0 || load[w] < load[best]) best = w;
+        }
+        // a partner of the same fit and segment with (almost) the same load wins
+        for (int w = 0; w < R_CWARPS; ++w)
+            if (cnt[w] == 1 && g.warp_half[w][0].fit == h.fit && g.warp_half[w][0].seg == h.seg && best >= 0 &&
+                load[w] <= load[best] + 2)
+                best = w;
+        if (best < 0) return;  // cannot happen: the caller admits at most 2 R_CWARPS halves
+        g.warp_half[best][cnt[best]++] = h;
+        load[best] += h.load;
+    }
+}
 
-// Which fits share a CTA and which Gram tiles each of its MMA warps owns.  Fits of one problem are
-// sorted by list width; a list whose bins exceed one CTA's eight MMA warps is split over several CTAs
-// that stage the same rows (the first leads: it alone evaluates the sums); the others are packed
-// first-fit, up to `fmax` fits per CTA; finally a group's tiles are re-dealt with the smallest load bound
-// that still fits eight warps.  Returns -1 for a list the tile numbering cannot hold.
+// Which fits share a CTA.  Fits of one problem are sorted by list width; a list with more halves than one
+// CTA holds is split over several CTAs that stage the same rows (the first leads: it alone evaluates the
+// sums); the others are packed first-fit, up to `fmax` fits and 2 R_CWARPS halves per CTA.
+// Returns -1 for a list the tile numbering cannot hold.
 int build_groups(int P, const std::vector<int> &prob_of, const std::vector<int> &live, const std::vector<int> &nGs,
                  int fmax, std::vector<Group> &groups) {
     const int nfits = (int)prob_of.size();
-    std::vector<Bin> bins;
+    const int cap = 2 * R_CWARPS;
+    std::vector<Half> hv;
     std::vector<int> order;
     for (int p = 0; p < P; ++p) {
         order.clear();
@@ -698,61 +768,56 @@ int build_groups(int P, const std::vector<int> &prob_of, const std::vector<int> 
         for (int f : order) {
             const int nG = nGs[f];
             if (nG < 0 || nG > 255 * 8) return -1;
-            const int ntr = (nG + 7) / 8, tiles = ntr * (ntr + 1) / 2;
-            pack_bins(ntr, 16, bins);
-            if ((int)bins.size() > R_CWARPS) {
-                for (size_t b0 = 0; b0 < bins.size(); b0 += R_CWARPS) {
+            const int ntr = (nG + 7) / 8;
+            hv.clear();
+            make_halves(0, ntr, hv);
+            if ((int)hv.size() > cap) {
+                for (size_t b0 = 0; b0 < hv.size(); b0 += cap) {
                     Group g;
                     g.prob = p; g.nfit = 1; g.fit[0] = f; g.lead[0] = (b0 == 0);
-                    for (size_t b = b0; b < bins.size() && b < b0 + R_CWARPS; ++b) {
-                        g.bins.emplace_back(0, bins[b]);
-                        g.tiles += bins[b].load;
+                    for (size_t b = b0; b < hv.size() && b < b0 + cap; ++b) {
+                        g.halves.push_back(hv[b]);
+                        g.tiles += hv[b].load;
                     }
+                    deal_halves(g);
                     groups.push_back(g);
                 }
                 continue;
             }
             bool placed = false;
             for (Group &g : open)
-                if (g.nfit < fmax && (int)g.bins.size() + (int)bins.size() <= R_CWARPS) {
+                if (g.nfit < fmax && (int)g.halves.size() + (int)hv.size() <= cap) {
                     const int sl = g.nfit++;
                     g.fit[sl] = f; g.lead[sl] = 1;
-                    for (auto &b : bins) g.bins.emplace_back(sl, b);
-                    g.tiles += tiles;
+                    for (Half h : hv) {
+                        h.fit = sl;
+                        g.halves.push_back(h);
+                        g.tiles += h.load;
+                    }
                     placed = true;
                     break;
                 }
             if (!placed) {
                 Group g;
                 g.prob = p; g.nfit = 1; g.fit[0] = f; g.lead[0] = 1;
-                for (auto &b : bins) g.bins.emplace_back(0, b);
-                g.tiles = tiles;
+                for (Half h : hv) {
+                    g.halves.push_back(h);
+                    g.tiles += h.load;
+                }
                 open.push_back(g);
             }
         }
         for (Group &g : open) {
-            if (g.tiles > 0 && (int)g.bins.size() < R_CWARPS) {
-                for (int T = std::max(4, (g.tiles + R_CWARPS - 1) / R_CWARPS); T < 16; ++T) {
-                    std::vector<std::pair<int, Bin>> nb;
-                    for (int sl = 0; sl < g.nfit; ++sl) {
-                        pack_bins((nGs[g.fit[sl]] + 7) / 8, T, bins);
-                        for (auto &b : bins) nb.emplace_back(sl, b);
-                    }
-                    if ((int)nb.size() <= R_CWARPS) {
-                        g.bins.swap(nb);
-                        break;
-                    }
-                }
-            }
+            deal_halves(g);
             groups.push_back(g);
         }
     }
     return 0;
 }
 
-unsigned bin_x(int fitslot, const Bin &bn) { return (unsigned)fitslot | ((unsigned)bn.seg << 8) | ((unsigned)bn.cnt << 16); }
-unsigned bin_y(const Bin &bn) {
-    return (unsigned)bn.rows[0] | ((unsigned)bn.rows[1] << 8) | ((unsigned)bn.rows[2] << 16) | ((unsigned)bn.rows[3] << 24);
+// descriptor of a half: fit slot | segment << 2 | count << 8 | row0 << 10 | row1 << 18
+unsigned half_word(const Half &h) {
+    return (unsigned)h.fit | ((unsigned)h.seg << 2) | ((unsigned)h.cnt << 8) | ((unsigned)h.rows[0] << 10) | ((unsigned)h.rows[1] << 18);
 }
 
 template <int ROWS, int ITER, int FMAX>
@@ -803,9 +868,9 @@ extern "C" int ate_round_plan_describe(int nfit, const int *list_cols, int stage
             d[1 + sl] = (unsigned)g.fit[sl];
             d[5] |= (unsigned)(g.lead[sl] ? 1 : 0) << sl;
         }
-        for (size_t b = 0; b < g.bins.size(); ++b) {
-            d[8 + 2 * b] = bin_x(g.bins[b].first, g.bins[b].second);
-            d[9 + 2 * b] = bin_y(g.bins[b].second);
+        for (int w = 0; w < R_CWARPS; ++w) {
+            d[8 + 2 * w] = half_word(g.warp_half[w][0]);
+            d[9 + 2 * w] = half_word(g.warp_half[w][1]);
         }
     }
     return (int)groups.size();
@@ -817,6 +882,8 @@ static size_t round_fixed_smem(int ncs, int fmax) {
     return sizeof(double) * (size_t)fmax * ncs + sizeof(int) * (size_t)(ncs / 4 + 4) + 2048;
 }
 static int round_rows_for(int ncs, int fmax) {
+    static const int forced = getenv("ATE_ROUND_ROWS") ? atoi(getenv("ATE_ROUND_ROWS")) : 0;  // A/B measurements
+    if ((forced == 16 || forced == 32) && (ncs + 63) / 64 == 5) return forced;
     const size_t b32 = sizeof(double) * ((size_t)32 * (ncs + R_PAD) + 2 * (size_t)fmax * 32);
     return (R_SMEM_LIMIT - round_fixed_smem(ncs, fmax)) / b32 >= 3 ? 32 : 16;
 }
@@ -857,42 +924,35 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
         *packed_count = 0;
         return 0;
     }
-    // ---- row chunks per group: the SMs are dealt in proportion to the estimated work ----
+    // ---- row chunks: every CTA kind of a problem cuts the problem's rows the same way (so that the CTAs of
+    //      a chunk, scheduled together, walk the same rows and the L2 serves the repeats).  About three
+    //      waves of CTAs are laid out, the work of a problem deciding its share: the hardware scheduler
+    //      then evens out CTA kinds of different cost, and no SM idles because 148 does not divide evenly.
+    std::vector<double> pcost(P, 0.0);
+    std::vector<int> pkinds(P, 0), pchunks(P, 1);
     double total_cost = 0.0;
     for (Group &g : groups) {
         int wmax = 0;
-        for (auto &b : g.bins) wmax = std::max(wmax, b.second.load);
+        for (int w = 0; w < R_CWARPS; ++w) wmax = std::max(wmax, g.warp_half[w][0].load + g.warp_half[w][1].load);
         g.cost = (double)probs[g.prob].nrows * (30.0 + 25.0 * g.nfit + 4.0 * wmax + 0.5 * g.tiles);
+        pcost[g.prob] += g.cost;
+        pkinds[g.prob]++;
         total_cost += g.cost;
     }
-    const int budget = std::max(ctx->num_sms, (int)groups.size());
-    int used = 0;
-    for (Group &g : groups) {
-        long long maxc = (probs[g.prob].nrows + 4LL * ROWS - 1) / (4LL * ROWS);
-        if (maxc < 1) maxc = 1;
-        int c = (int)(g.cost / total_cost * budget);
-        if (c < 1) c = 1;
-        if (c > maxc) c = (int)maxc;
-        g.chunks = c;
-        used += c;
-    }
-    for (bool grew = true; used < budget && grew;) {  // hand out the remainder to the most loaded groups
-        grew = false;
-        Group *best = nullptr;
-        for (Group &g : groups) {
-            const long long maxc = std::max(1LL, (probs[g.prob].nrows + 4LL * ROWS - 1) / (4LL * ROWS));
-            if (g.chunks >= maxc) continue;
-            if (!best || g.cost / g.chunks > best->cost / best->chunks) best = &g;
-        }
-        if (best) {
-            best->chunks++;
-            used++;
-            grew = true;
+    {
+        static const int waves = getenv("ATE_ROUND_WAVES") ? std::max(1, atoi(getenv("ATE_ROUND_WAVES"))) : 3;
+        const double budget = (double)waves * ctx->num_sms;
+        for (int p = 0; p < P; ++p) {
+            if (!pkinds[p]) continue;
+            long long maxc = (probs[p].nrows + 16LL * ROWS - 1) / (16LL * ROWS);  // at least 16 slots per CTA
+            if (maxc < 1) maxc = 1;
+            long long c = (long long)(pcost[p] / total_cost * budget / pkinds[p] + 0.5);
+            if (c < 1) c = 1;
+            if (c > maxc) c = maxc;
+            pchunks[p] = (int)c;
         }
     }
-    // all CTAs of one fit must cut the rows the same way (they write the same partial slots)
-    for (size_t i = 0; i < groups.size(); ++i)
-        if (!groups[i].lead[0] && i > 0) groups[i].chunks = groups[i - 1].chunks;
+    for (Group &g : groups) g.chunks = pchunks[g.prob];
 
     // ---- per-fit outputs: partial slots and the packed result buffer ----
     slots.assign(nfits, RoundSlot{0, 0, 0});
@@ -968,26 +1028,31 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
     }
     RoundStats st;
     int ci = 0;
+    for (int p = 0; p < P; ++p) {
+        if (!pkinds[p]) continue;
+        const long long nrows = probs[p].nrows;
+        long long rpc = (nrows + pchunks[p] - 1) / pchunks[p];
+        rpc = (rpc + ROWS - 1) / ROWS * ROWS;
+        for (int c = 0; c < pchunks[p]; ++c)          // chunk-major: the kinds of a chunk sit side by side
+            for (Group &g : groups) {
+                if (g.prob != p) continue;
+                DCta &d = hc[ci++];
+                d.prob = g.prob;
+                d.nfit = g.nfit;
+                d.chunk = c;
+                d.row_begin = std::min(nrows, (long long)c * rpc);
+                d.row_end = std::min(nrows, (long long)(c + 1) * rpc);
+                for (int sl = 0; sl < g.nfit; ++sl) {
+                    d.fit[sl] = g.fit[sl];
+                    d.lead[sl] = g.lead[sl];
+                }
+                for (int wq = 0; wq < R_CWARPS; ++wq)
+                    d.mma[wq] = make_uint2(half_word(g.warp_half[wq][0]), half_word(g.warp_half[wq][1]));
+                st.rows_staged += d.row_end - d.row_begin;
+            }
+    }
     for (Group &g : groups) {
         const long long nrows = probs[g.prob].nrows;
-        long long rpc = (nrows + g.chunks - 1) / g.chunks;
-        rpc = (rpc + ROWS - 1) / ROWS * ROWS;
-        for (int c = 0; c < g.chunks; ++c, ++ci) {
-            DCta &d = hc[ci];
-            d.prob = g.prob;
-            d.nfit = g.nfit;
-            d.chunk = c;
-            d.row_begin = std::min(nrows, (long long)c * rpc);
-            d.row_end = std::min(nrows, (long long)(c + 1) * rpc);
-            for (int sl = 0; sl < g.nfit; ++sl) {
-                d.fit[sl] = g.fit[sl];
-                d.lead[sl] = g.lead[sl];
-            }
-            for (size_t b = 0; b < g.bins.size() && b < (size_t)R_CWARPS; ++b) {
-                d.mma[b] = make_uint2(bin_x(g.bins[b].first, g.bins[b].second), bin_y(g.bins[b].second));
-            }
-            st.rows_staged += d.row_end - d.row_begin;
-        }
         for (int sl = 0; sl < g.nfit; ++sl)
             if (g.lead[sl]) {
                 const double nG = fits[g.fit[sl]].nG;
@@ -1005,9 +1070,9 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
             for (size_t gi = 0; gi < groups.size() && gi < 12; ++gi) {
                 const Group &g = groups[gi];
                 int wmax = 0;
-                for (auto &b : g.bins) wmax = std::max(wmax, b.second.load);
-                fprintf(stderr, "   kind %zu: prob %d fits %d (nG %d, %d) lead %d bins %zu tiles %d busiest %d chunks %d rows/chunk %lld\n", gi,
-                        g.prob, g.nfit, fits[g.fit[0]].nG, g.nfit > 1 ? fits[g.fit[1]].nG : -1, g.lead[0], g.bins.size(), g.tiles, wmax,
+                for (int w = 0; w < R_CWARPS; ++w) wmax = std::max(wmax, g.warp_half[w][0].load + g.warp_half[w][1].load);
+                fprintf(stderr, "   kind %zu: prob %d fits %d (nG %d, %d) lead %d halves %zu tiles %d busiest %d chunks %d rows/chunk %lld\n", gi,
+                        g.prob, g.nfit, fits[g.fit[0]].nG, g.nfit > 1 ? fits[g.fit[1]].nG : -1, g.lead[0], g.halves.size(), g.tiles, wmax,
                         g.chunks, (long long)((probs[g.prob].nrows + g.chunks - 1) / g.chunks));
             }
         }
@@ -1022,7 +1087,9 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
     a.skip = ctx->debug_skip;
     {
         static const int hint = getenv("ATE_WAIT_HINT_NS") ? atoi(getenv("ATE_WAIT_HINT_NS")) : 0;
+        static const int rolemap = getenv("ATE_ROUND_ROLEMAP") ? atoi(getenv("ATE_ROUND_ROLEMAP")) : 0;
         a.wait_hint = hint;
+        a.rolemap = rolemap;
     }
     const DFold *dfolds = (const DFold *)((char *)ddesc + o_folds);
 

@@ -309,8 +309,9 @@ ATE_API int ate_cv_select(int nfolds, int lmu, const double *cvraw, const double
  * the number of CTA kinds G (<= max_groups, else -2), and desc[24 g + ...] describes kind g:
  *   [0] fits served (1 to 4), [1 .. 4] their indices, [5] bit s set when this kind evaluates the sums
  *   of its fit s (a list too wide for one CTA is split over several kinds; the first one leads),
- *   [8 + 2 w], [9 + 2 w] for MMA warp w = 0..7: x = fit slot | segment << 8 | count << 16, y = up to four
- *   tile-row numbers, one per byte (count 0: the warp idles).
+ *   [8 + 2 w], [9 + 2 w] for MMA warp w = 0..7: its two halves, each fit slot | segment << 2 |
+ *   count << 8 | row0 << 10 | row1 << 18 (a half = up to two tile rows of one 32-column segment of one
+ *   fit; count 0: none).
  * Lets tests check on a CPU-only box that every 8x8 tile of every fit's lower triangle is computed
  * exactly once for every mix of widths.  -1 for widths the step cannot take. */
 ATE_API int ate_round_plan_describe(int nfit, const int *list_cols, int staged_cols, int max_groups, unsigned *desc);

@@ -171,22 +171,22 @@ def _check_round_plan(lib, widths, staged):
             if (d[5] >> s) & 1:
                 leads[fits[s]] = leads.get(fits[s], 0) + 1
         for w in range(8):
-            x, y = d[8 + 2 * w], d[9 + 2 * w]
-            slot, seg, cnt = x & 0xFF, (x >> 8) & 0xFF, (x >> 16) & 0xFF
-            if cnt == 0:
-                continue
-            assert slot < nfit and 1 <= cnt <= 4
-            f = fits[slot]
-            ntr = (int(widths[f]) + 7) // 8
             tiles = 0
-            for u in range(cnt):
-                r = (y >> (8 * u)) & 0xFF
-                assert 4 * seg <= r < ntr
-                for n in range(min(4, r - 4 * seg + 1)):
-                    key = (f, r, 4 * seg + n)
-                    assert key not in owned, (widths, key)
-                    owned[key] = (g, w)
-                    tiles += 1
+            for word in (d[8 + 2 * w], d[9 + 2 * w]):          # two halves per MMA warp
+                slot, seg, cnt = word & 3, (word >> 2) & 63, (word >> 8) & 3
+                if cnt == 0:
+                    continue
+                assert slot < nfit and 1 <= cnt <= 2
+                f = fits[slot]
+                ntr = (int(widths[f]) + 7) // 8
+                for u in range(cnt):
+                    r = (word >> (10 + 8 * u)) & 255
+                    assert 4 * seg <= r < ntr
+                    for n in range(min(4, r - 4 * seg + 1)):
+                        key = (f, r, 4 * seg + n)
+                        assert key not in owned, (widths, key)
+                        owned[key] = (g, w)
+                        tiles += 1
             assert tiles <= 16
     want = {(f, r, c) for f in range(len(widths)) for r in range((int(widths[f]) + 7) // 8) for c in range(r + 1)}
     assert set(owned) == want, widths
@@ -202,8 +202,9 @@ def test_step_kernel_work_plan_covers_every_tile_once():
     lib = _lib.load()
     for cols in list(range(0, 130)) + [160, 200, 255, 256, 300, 412, 513, 1024]:
         _check_round_plan(lib, [cols], 264)
-    assert _check_round_plan(lib, [64] * 10, 264) == 5           # 36 tiles per fit: two fits fill a CTA's eight MMA warps
+    assert _check_round_plan(lib, [64] * 10, 264) == 5           # 36 tiles in six halves per fit: two fits fill a CTA's MMA warps
     assert _check_round_plan(lib, [32] * 10, 264) == 3           # 10 tiles per fit: four fits per CTA
+    assert _check_round_plan(lib, [40] * 10, 264) == 3           # lists up to 48 columns still share a CTA four ways
     assert _check_round_plan(lib, [64] * 10, 520) == 10          # wide rows (C4): one fit per CTA
     assert _check_round_plan(lib, [200], 264) >= 2                # a list too wide for one CTA is split
     rng = np.random.default_rng(3)

@@ -28,7 +28,7 @@ tests)
 alltests)
     step t_all 1500 python -m pytest tests -m gpu -x -q ;;
 rbench)
-    step round_bench 600 python tools/round_bench.py --cases 1x1,5x1,5x10 --lists 0,32,48,64,96 --skips 0,1,2,15 ;;
+    step round_bench 600 python tools/round_bench.py --cases 1x1,5x1,5x10 --lists 32,48,64,96,128 --skips 0 ;;
 ncu_rb)
     step ncu_rb 600 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 2 -c 1 -o gpurun_out/ncu_rb python tools/round_bench.py --cases 5x10 --lists 32 --skips 0 --iters 3
     ncu -i gpurun_out/ncu_rb.ncu-rep --page source --csv > gpurun_out/ncu_rb_source.csv 2>/dev/null
