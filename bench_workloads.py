@@ -118,7 +118,9 @@ def run_crossfit(c: BenchCtx):
         h2d = (n * p0 + 2 * n) * 8 + (n + 2 * K * n) * 4          # base covariates, w, y; outer + inner fold ids
         d2h = 3 * n * 8 + args.B * 8 + 2 * K * 8 + 208             # phat, m0, m1; replicates; lambdas; result struct
         e2e = dict(value=1e3 / (ms_e2e / args.steps), unit=B.UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
-                   ms_per_step=ms_e2e / args.steps)
+                   ms_per_step=ms_e2e / args.steps,
+                   stage_ms={k: last_h.get(k) for k in ("ms_design", "ms_folds", "ms_outcome", "ms_propensity", "ms_score",
+                                                        "ms_bootstrap")})
 
     roof = None
     if c.rank == 0:
@@ -138,7 +140,9 @@ def run_crossfit(c: BenchCtx):
                        staged_gb_per_fit=staged_gb)
         ten_obj = dict(achieved=tf, peak=peak_tensor, unit="TFLOP/s", frac=tf / peak_tensor if peak_tensor else None,
                        algorithmic="sum over the launch's live fits of rows * (|L| (|L| + 1) + 6 p) flop: the strong-set "
-                                   "Gram's lower triangle on DMMA plus eta, X^T r, X^T v on the FP64 FMA pipe",
+                                   "Gram's lower triangle plus eta, X^T r, X^T v; all of it issues as DMMA.8x8x4 "
+                                   "(CTAs serving a single fit run X^T r / X^T v on the FP64 FMA pipe). The padded tiles "
+                                   "the kernel really issues are about 2x this count",
                        peak_source="cuBLAS DGEMM 8192^3 measured in this run (MEASURED_PEAKS.json has no fp64 row)")
         primary = "tensor" if (ten_obj["frac"] or 0) >= hbm_obj["frac"] else "hbm"
         p_obj = ten_obj if primary == "tensor" else hbm_obj
@@ -147,8 +151,10 @@ def run_crossfit(c: BenchCtx):
                     achieved=p_obj["achieved"], peak=p_obj["peak"], unit=p_obj["unit"], frac=p_obj["frac"],
                     traffic=traffic, traffic_capture=cap, launches=prof["gram_launches"], avg_launch_ms=avg_ms,
                     share_of_step=prof["gram_ms"] / ms_prof, profiled_fit_ms=ms_prof, hbm=hbm_obj, tensor=ten_obj,
-                    note="both ceilings are reported: the step is an HBM stream of rows feeding fp64 FMA/DMMA work; "
-                         "`bound` names the ceiling it sits closer to")
+                    dram_gbs=(traffic / (avg_ms * 1e-3) / 1e9 if traffic and avg_ms > 0 else None),
+                    note="both ceilings are reported: the step is a stream of rows (HBM -> L2 -> shared memory by 1-D TMA) "
+                         "feeding fp64 DMMA work; `bound` names the ceiling the ALGORITHMIC figure sits closer to, "
+                         "`dram_gbs` is the measured DRAM traffic of one launch over the same duration")
 
     cpu = None
     one = None

@@ -38,10 +38,17 @@ trace)
       ATE_B200_LIB=$PWD/ate_replication_causalml_b200/libate_b200_trace.so ATE_ROUND_TRACE_OUT=gpurun_out/trace_$tag.csv step trace_$tag 300 python tools/round_bench.py --cases $1 --lists $2 --skips 0 --iters 2
       python tools/round_trace.py gpurun_out/trace_$tag.csv 60 76
     done ;;
+hbm)
+    step hbm_passes 600 python tools/hbm_passes.py ;;
+ncu_hbm)
+    step ncu_hbm 900 ncu --set full --clock-control none --import-source on -k regex:'col_moments_kernel|col_apply|build_design|expand_col|aipw_score|bootstrap_kernel|gather_rows|cvdev|predict_rows|rk_rank|rk_hist|scatter_kernel|inner_key' -c 40 -o gpurun_out/ncu_hbm python tools/hbm_passes.py
+    ncu -i gpurun_out/ncu_hbm.ncu-rep --page raw --csv > gpurun_out/ncu_hbm_raw.csv 2>/dev/null ;;
+sass)
+    cuobjdump -sass ate_replication_causalml_b200/libate_b200.so > gpurun_out/libate_b200.sass 2>/dev/null ;;
 smoke)
     step smoke 300 python -c "import __graft_entry__ as g; g.smoke()" ;;
 bench)
-    ATE_TIMING=1 step bench_c1 900 python bench.py --steps 2 --warmup 2
+    step bench_c1 900 python bench.py --steps 2 --warmup 3
     grep -h '^{' gpurun_out/bench_c1.log | tail -1 > gpurun_out/bench_c1.json ;;
 benchq)
     ATE_PROFILE_CSV=gpurun_out/round_launches.csv ATE_ROUND_DEBUG=1 step bench_c1q 600 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e
@@ -59,7 +66,21 @@ c4)
     step bench_c4 1500 python bench.py --workload C4 --steps 1 --warmup 1 --no-e2e
     grep -h '^{' gpurun_out/bench_c4.log | tail -1 > gpurun_out/bench_c4.json ;;
 ncu_list)
-    step ncu_launches 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --steps 1 --warmup 0 --n 200000 --no-cpu-baseline --no-e2e ;;
+    step ncu_launches 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e ;;
+mgcheck)
+    NG=${NGPU:-2}
+    step mg${NG}_check 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29511 tools/multi_gpu_check.py ;;
+mgbench)
+    NG=${NGPU:-2}
+    step bench_c1_n$NG 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $NG --steps 2 --warmup 3
+    grep -h '^{' gpurun_out/bench_c1_n$NG.log | tail -1 > gpurun_out/bench_c1_n$NG.json ;;
+mgref)
+    NG=${NGPU:-2}
+    step bench_ref_n$NG 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29513 bench.py --impl reference --gpus $NG --steps 1 --warmup 1 ;;
+mgc4)
+    NG=${NGPU:-2}
+    step bench_c4_n$NG 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29514 bench.py --gpus $NG --workload C4 --steps 1 --warmup 1 --no-e2e
+    grep -h '^{' gpurun_out/bench_c4_n$NG.log | tail -1 > gpurun_out/bench_c4_n$NG.json ;;
 ncu_round)
     step ncu_round 900 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 150 -c 3 -o gpurun_out/ncu_round python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e ;;
 *)
