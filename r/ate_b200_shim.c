@@ -143,8 +143,10 @@ SEXP C_ate_expand_deg2(SEXP ctx, SEXP x) {
 }
 
 /* the composite: K-fold cross-fitted AIPW + bootstrap   */
+/* shard: NULL, or c(rank, count) when the rows of this fit are shared by `count` R processes (one per
+ * GPU, each after C_ate_ctx_nccl_init); every process passes the same full inputs and gets the full row */
 SEXP C_ate_crossfit_aipw(SEXP ctx, SEXP x, SEXP w, SEXP y, SEXP K, SEXP B, SEXP seed, SEXP foldid,
-                         SEXP inner_ps, SEXP inner_out, SEXP boot_idx, SEXP expand, SEXP ncont) {
+                         SEXP inner_ps, SEXP inner_out, SEXP boot_idx, SEXP expand, SEXP ncont, SEXP shard) {
     ate_ctx *c = ctx_of(ctx);
     ate_crossfit_opts o;
     ate_crossfit_default_opts(&o);
@@ -152,6 +154,7 @@ SEXP C_ate_crossfit_aipw(SEXP ctx, SEXP x, SEXP w, SEXP y, SEXP K, SEXP B, SEXP 
     o.r_seed = (uint32_t)Rf_asInteger(seed); o.boot_seed = (uint64_t)Rf_asInteger(seed);
     o.expand = Rf_asInteger(expand); o.n_continuous = Rf_asInteger(ncont); o.standardize_base = o.n_continuous > 0;
     o.boot_mode = Rf_isNull(boot_idx) ? ATE_BOOT_PHILOX : ATE_BOOT_INDEX;
+    if (!Rf_isNull(shard)) { o.shard_rank = INTEGER(shard)[0]; o.shard_count = INTEGER(shard)[1]; }
     ate_crossfit_result r;
     int rc = ate_crossfit_aipw(c, &o, Rf_nrows(x), Rf_ncols(x), REAL(x), REAL(w), REAL(y),
                                Rf_isNull(foldid) ? NULL : INTEGER(foldid),
@@ -189,6 +192,23 @@ SEXP C_ate_lm(SEXP ctx, SEXP x, SEXP y, SEXP weights, SEXP want_resid) {
     return tab;
 }
 
+/* Multi-GPU (no reference counterpart): rank 0 mints the 128-byte NCCL id, the R driver ships it to
+ * the other processes (Rmpi::mpi.bcast of the raw vector, or a file), every process then joins. */
+SEXP C_ate_nccl_unique_id(void) {
+    SEXP id = PROTECT(Rf_allocVector(RAWSXP, 128));
+    int rc = ate_nccl_unique_id((char *)RAW(id));
+    UNPROTECT(1);
+    if (rc != 0) Rf_error("ate_nccl_unique_id: libnccl.so.2 could not be loaded");
+    return id;
+}
+SEXP C_ate_ctx_nccl_init(SEXP ctx, SEXP id, SEXP rank, SEXP nranks) {
+    ate_ctx *c = ctx_of(ctx);
+    if (XLENGTH(id) != 128) Rf_error("ate_ctx_nccl_init: id must be the 128 raw bytes of C_ate_nccl_unique_id");
+    int rc = ate_ctx_nccl_init(c, (const char *)RAW(id), Rf_asInteger(rank), Rf_asInteger(nranks));
+    FAIL_IF(rc, c, "ate_ctx_nccl_init");
+    return R_NilValue;
+}
+
 static const R_CallMethodDef call_methods[] = {
     {"C_ate_ctx_create", (DL_FUNC)&C_ate_ctx_create, 1},
     {"C_ate_cv_glmnet", (DL_FUNC)&C_ate_cv_glmnet, 8},
@@ -200,7 +220,9 @@ static const R_CallMethodDef call_methods[] = {
     {"C_ate_tau_hat_dr_est", (DL_FUNC)&C_ate_tau_hat_dr_est, 7},
     {"C_ate_standardize", (DL_FUNC)&C_ate_standardize, 2},
     {"C_ate_expand_deg2", (DL_FUNC)&C_ate_expand_deg2, 2},
-    {"C_ate_crossfit_aipw", (DL_FUNC)&C_ate_crossfit_aipw, 13},
+    {"C_ate_crossfit_aipw", (DL_FUNC)&C_ate_crossfit_aipw, 14},
+    {"C_ate_nccl_unique_id", (DL_FUNC)&C_ate_nccl_unique_id, 0},
+    {"C_ate_ctx_nccl_init", (DL_FUNC)&C_ate_ctx_nccl_init, 4},
     {NULL, NULL, 0}};
 
 void R_init_ateb200(DllInfo *dll) {

@@ -151,15 +151,28 @@ doubly_robust_glm <- function(dataset, treatment_var, outcome_var, bootstrap_se 
 # the composite of SURVEY.md section 8 (new; the reference's only sample-splitting precedent is :372-389)
 crossfit_aipw <- function(dataset, treatment_var, outcome_var, bootstrap_se = T, B = 1000, K = 5,
                           seed = 1991, foldid = NULL, inner_ps = NULL, inner_out = NULL, boot_idx = NULL,
-                          expand = 0L, n_continuous = 0L) {
+                          expand = 0L, n_continuous = 0L, shard = NULL) {
+  # shard = c(rank, count): the rows of this ONE fit are shared by `count` R processes, one per GPU,
+  # each of which called ate_join_ranks() first and passes the same dataset; all get the same row back
   x <- as.matrix(dataset[covariates]); storage.mode(x) <- "double"
   asint <- function(m) if (is.null(m)) NULL else { d <- dim(m); m <- as.integer(m); dim(m) <- d; m }
   foldid <- asint(foldid); inner_ps <- asint(inner_ps); inner_out <- asint(inner_out)
   boot_idx <- asint(boot_idx)            # n x B, one replicate per column (see .dr_tail)
   r <- .Call("C_ate_crossfit_aipw", ate_ctx(), x, as.double(dataset[, treatment_var]),
              as.double(dataset[, outcome_var]), as.integer(K), as.integer(if (bootstrap_se) B else 0L),
-             as.integer(seed), foldid, inner_ps, inner_out, boot_idx, as.integer(expand), as.integer(n_continuous))
+             as.integer(seed), foldid, inner_ps, inner_out, boot_idx, as.integer(expand), as.integer(n_continuous),
+             if (is.null(shard)) NULL else as.integer(shard))
   se <- if (bootstrap_se) r[3] else r[2]
   data.frame(Method = "Cross-fitted AIPW with glmnet nuisances", ATE = r[1],
              lower_ci = r[1] - 1.96 * se, upper_ci = r[1] + 1.96 * se)
+}
+
+# Multi-GPU: one R process per GPU (mpirun -np G Rscript ...).  Rank 0 mints the NCCL id, Rmpi carries
+# the 128 raw bytes, every process joins; the library then sums its per-round partials over the ranks
+# on its own stream (include/ate_b200.h: ate_nccl_unique_id, ate_ctx_nccl_init).
+ate_join_ranks <- function(rank = Rmpi::mpi.comm.rank(0), count = Rmpi::mpi.comm.size(0)) {
+  id <- if (rank == 0) .Call("C_ate_nccl_unique_id") else raw(128)
+  id <- Rmpi::mpi.bcast(id, type = 4, rank = 0, comm = 0)     # type 4: raw
+  .Call("C_ate_ctx_nccl_init", ate_ctx(), id, as.integer(rank), as.integer(count))
+  c(rank, count)
 }

@@ -10,6 +10,7 @@ typedef enum { FALSE = 0, TRUE } Rboolean;
 #define INTSXP 13
 #define REALSXP 14
 #define VECSXP 19
+#define RAWSXP 24
 extern SEXP R_NilValue;
 extern double R_NaReal;
 #define NA_REAL R_NaReal
@@ -20,6 +21,7 @@ void Rf_unprotect(int);
 #define UNPROTECT(n) Rf_unprotect(n)
 double *REAL(SEXP);
 int *INTEGER(SEXP);
+unsigned char *RAW(SEXP);
 R_xlen_t XLENGTH(SEXP);
 SEXP Rf_allocVector(SEXPTYPE, R_xlen_t);
 SEXP Rf_allocMatrix(SEXPTYPE, int, int);

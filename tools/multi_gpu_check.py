@@ -14,22 +14,31 @@ rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); lr = int(
 torch.cuda.set_device(lr)
 dev = torch.device("cuda", lr)
 dist.init_process_group("nccl", device_id=dev)
-n, p0 = int(os.environ.get("ATE_CHECK_N", "20000")), 8
-d = synth.make_dataset(n, p0)
-fo, ips, iout = make_folds(n)
 eng = Engine(lr)
 comm = parallel.TorchComm(dist, dev)
-kw = dict(n_continuous=d["n_continuous"], expand=1, B=200, nlambda=100, want_nuisances=True)
-r = parallel.crossfit_sharded(eng, d["x_raw"], d["w"], d["y"], n, p0, fo, ips, iout, comm=comm, on_device=False, **kw)
-ref = parallel.crossfit_sharded(eng, d["x_raw"], d["w"], d["y"], n, p0, fo, ips, iout, comm=None, on_device=False, **kw)
 rel = lambda a, b: abs(a - b) / abs(b)
-ok = (rel(r["tau"], ref["tau"]) < 1e-9 and rel(r["se_sandwich"], ref["se_sandwich"]) < 1e-9
-      and rel(r["se_bootstrap"], ref["se_bootstrap"]) < 1e-9 and np.allclose(r["lambda_ps"], ref["lambda_ps"], rtol=1e-9)
-      and np.allclose(r["lambda_out"], ref["lambda_out"], rtol=1e-9) and np.abs(r["phat"] - ref["phat"]).max() < 1e-9
-      and np.abs(r["m0"] - ref["m0"]).max() < 1e-9)
-print(f"rank {rank}/{world}: shared tau {r['tau']:.15f} se_b {r['se_bootstrap']:.15f} | single tau {ref['tau']:.15f} "
-      f"se_b {ref['se_bootstrap']:.15f} | max |dphat| {np.abs(r['phat'] - ref['phat']).max():.2e} | agree={ok}", flush=True)
+all_ok = True
+# (a) a twin-free design (no products): the shared fit follows the same iterates, so 1e-9;
+# (b) the benchmark's ordered products (twin columns x_i x_j / x_j x_i): rounding in the summed moments may
+#     admit the other twin, the fitted values then agree to the convergence threshold -- the 1e-6 bar.
+for tag, n, p0, expand, tol in (("twin-free", int(os.environ.get("ATE_CHECK_N", "20000")), 12, 0, 1e-9),
+                                ("products", int(os.environ.get("ATE_CHECK_N", "20000")), 8, 1, 1e-6)):
+    d = synth.make_dataset(n, p0)
+    fo, ips, iout = make_folds(n)
+    kw = dict(n_continuous=d["n_continuous"], expand=expand, B=200, nlambda=100, want_nuisances=True)
+    r = parallel.crossfit_sharded(eng, d["x_raw"], d["w"], d["y"], n, p0, fo, ips, iout, comm=comm, on_device=False, **kw)
+    ref = parallel.crossfit_sharded(eng, d["x_raw"], d["w"], d["y"], n, p0, fo, ips, iout, comm=None, on_device=False, **kw)
+    diffs = dict(tau=rel(r["tau"], ref["tau"]), se=rel(r["se_sandwich"], ref["se_sandwich"]),
+                 se_boot=rel(r["se_bootstrap"], ref["se_bootstrap"]),
+                 lam_ps=float(np.abs(r["lambda_ps"] / ref["lambda_ps"] - 1).max()),
+                 lam_out=float(np.abs(r["lambda_out"] / ref["lambda_out"] - 1).max()),
+                 phat=float(np.abs(r["phat"] - ref["phat"]).max()), m0=float(np.abs(r["m0"] - ref["m0"]).max()),
+                 m1=float(np.abs(r["m1"] - ref["m1"]).max()))
+    ok = all(v < tol for v in diffs.values())
+    all_ok &= ok
+    print(f"rank {rank}/{world} {tag} n={n} p0={p0} expand={expand}: tau {r['tau']:.15f} vs {ref['tau']:.15f} | "
+          + " ".join(f"{k}={v:.1e}" for k, v in diffs.items()) + f" | tol {tol:g} agree={ok}", flush=True)
 dist.barrier()
 eng.close()
 dist.destroy_process_group()
-sys.exit(0 if ok else 1)
+sys.exit(0 if all_ok else 1)
