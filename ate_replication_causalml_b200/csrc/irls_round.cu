@@ -140,6 +140,32 @@ __device__ long long g_rtrace[TR_SLOTS * TR_EVENTS + 8];
 #define RTRACE(ev, it) do { } while (0)
 #endif
 
+// One slot of one HALF of an MMA warp: tile rows a (NA tiles) and b (NB <= NA tiles) of one 32-column
+// segment, all k-steps of the slot.  NA / NB are compile-time so that the loop body is straight-line
+// DMMAs: a run-time tile count inside the loop costs a jump table and a WARPSYNC per tile row and
+// k-step (measured: more than half of the MMA warps' issue slots).  sbase: the slot's rows (shared
+// memory, bytes); the operand offsets are per-lane byte offsets into a row, row k4 of each k-step.
+template <int NA, int NB, int ROWS>
+__device__ __forceinline__ void mma_half_slot(double (&accA)[4][2], double (&accB)[4][2], const char *sbase, uint32_t kstep_bytes,
+                                              const double *vs, uint32_t offA0, uint32_t offA1, const uint32_t (&offB)[4]) {
+#pragma unroll 2
+    for (int kk = 0; kk < ROWS / 4; ++kk) {
+        const char *rowp = sbase + (size_t)kk * kstep_bytes;  // (warp-uniform)
+        const double vv = vs[kk * 4];
+        double fb[NA];
+#pragma unroll
+        for (int n = 0; n < NA; ++n) fb[n] = *reinterpret_cast<const double *>(rowp + offB[n]) * vv;
+        const double fa = *reinterpret_cast<const double *>(rowp + offA0);
+#pragma unroll
+        for (int n = 0; n < NA; ++n) dmma884(accA[n][0], accA[n][1], fa, fb[n]);
+        if (NB > 0) {
+            const double fa1 = *reinterpret_cast<const double *>(rowp + offA1);
+#pragma unroll
+            for (int n = 0; n < NB; ++n) dmma884(accB[n][0], accB[n][1], fa1, fb[n]);
+        }
+    }
+}
+
 template <int ROWS, int ITER, int FMAX, bool INIT>
 __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a) {
     constexpr int PSHARE = ROWS / R_PWARPS;      // rows of a slot staged by one producer (row-list mode)
@@ -546,7 +572,8 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         // two halves per warp; a half = up to two tile rows of one 32-column segment of one fit
         const uint2 d = scta.mma[warp];
         const int g = lane >> 2, k4 = lane & 3;
-        int fsl[2], seg[2], nt[4], tr[4], offA[4], offB[2][4];
+        int fsl[2], seg[2], nt[4], tr[4], pat[2];
+        uint32_t offA[4], offB[2][4];  // per-lane byte offsets into a staged row (row k4 of a k-step folded in)
         bool any = false;
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
@@ -561,13 +588,15 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
                 tr[u] = (int)((wd >> (10 + 8 * j)) & 255u);
                 const int lim = tr[u] - 4 * seg[hh] + 1;  // tiles left of (and on) the diagonal in this segment
                 nt[u] = j < cnt ? (lim < 4 ? lim : 4) : 0;
-                offA[u] = nt[u] > 0 ? __ldg(colidx + tr[u] * 8 + g) : 0;
+                offA[u] = (uint32_t)((nt[u] > 0 ? __ldg(colidx + tr[u] * 8 + g) : 0) + k4 * pitch) * 8u;
             }
 #pragma unroll
-            for (int n = 0; n < 4; ++n) offB[hh][n] = cnt > 0 ? __ldg(colidx + (4 * seg[hh] + n) * 8 + g) : 0;
+            for (int n = 0; n < 4; ++n)
+                offB[hh][n] = (uint32_t)((cnt > 0 ? __ldg(colidx + (4 * seg[hh] + n) * 8 + g) : 0) + k4 * pitch) * 8u;
             any |= cnt > 0;
+            pat[hh] = nt[2 * hh] * 5 + nt[2 * hh + 1];  // the planner puts the heavier tile row first
         }
-        const bool same = (fsl[0] == fsl[1] && seg[0] == seg[1]);  // both halves read the same B operands
+        const uint32_t kstep_bytes = (uint32_t)pitch * 32u;  // four rows per k-step
         double acc[4][4][2];
 #pragma unroll
         for (int u = 0; u < 4; ++u)
@@ -580,43 +609,26 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             if (any && !(a.skip & 1)) {
                 wait_g(vfull + s, ph, whint);
                 if (warp < 3) RTRACE(9 + 2 * warp, it);  // MMA warp 0..2: start
-                const double *base = sx + stage_doubles * s;
-                const double *vs0 = sv + ((size_t)s * FMAX + fsl[0]) * ROWS, *vs1 = sv + ((size_t)s * FMAX + fsl[1]) * ROWS;
-#pragma unroll 1
-                for (int kk = 0; kk < ROWS / 4; ++kk) {
-                    const int r = kk * 4 + k4;
-                    const double *rowp = base + (size_t)r * pitch;
-                    double fb[4];
+                const char *sbase = reinterpret_cast<const char *>(sx + stage_doubles * s);
 #pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) {
-                        if (hh == 0 || !same) {  // (warp-uniform)
-                            const double vv = hh ? vs1[r] : vs0[r];
-#pragma unroll
-                            for (int n = 0; n < 4; ++n) fb[n] = rowp[offB[hh][n]] * vv;
-                        }
-#pragma unroll
-                        for (int j = 0; j < 2; ++j) {
-                            // one (warp-uniform) branch per tile row, then straight-line MMAs: a guard on every
-                            // mma.sync would cost a re-convergence barrier per instruction
-                            const int u = 2 * hh + j;
-                            const double fa = rowp[offA[u]];
-                            if (nt[u] == 4) {
-                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
-                                dmma884(acc[u][1][0], acc[u][1][1], fa, fb[1]);
-                                dmma884(acc[u][2][0], acc[u][2][1], fa, fb[2]);
-                                dmma884(acc[u][3][0], acc[u][3][1], fa, fb[3]);
-                            } else if (nt[u] == 3) {
-                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
-                                dmma884(acc[u][1][0], acc[u][1][1], fa, fb[1]);
-                                dmma884(acc[u][2][0], acc[u][2][1], fa, fb[2]);
-                            } else if (nt[u] == 2) {
-                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
-                                dmma884(acc[u][1][0], acc[u][1][1], fa, fb[1]);
-                            } else if (nt[u] == 1) {
-                                dmma884(acc[u][0][0], acc[u][0][1], fa, fb[0]);
-                            }
-                        }
+                for (int hh = 0; hh < 2; ++hh) {
+                    const double *vs = sv + ((size_t)s * FMAX + fsl[hh]) * ROWS + k4;
+                    // one (warp-uniform) dispatch per half and slot, then straight-line loops
+#define MMA_HALF(NA_, NB_)                                                                                          \
+    case (NA_) * 5 + (NB_):                                                                                          \
+        mma_half_slot<NA_, NB_, ROWS>(acc[2 * hh], acc[2 * hh + 1], sbase, kstep_bytes, vs, offA[2 * hh], offA[2 * hh + 1], \
+                                      offB[hh]);                                                                     \
+        break;
+                    switch (pat[hh]) {
+                        MMA_HALF(4, 4) MMA_HALF(4, 3) MMA_HALF(4, 2) MMA_HALF(4, 1) MMA_HALF(4, 0)
+                        MMA_HALF(3, 2) MMA_HALF(3, 1) MMA_HALF(3, 0)
+                        MMA_HALF(2, 1) MMA_HALF(2, 0)
+                        MMA_HALF(1, 0)
+                        default:
+                            if (pat[hh] != 0) __trap();  // not a pair the planner deals (an empty half is 0)
+                            break;
                     }
+#undef MMA_HALF
                 }
             }
             __syncwarp();

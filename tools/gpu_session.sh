@@ -32,7 +32,8 @@ rbench)
 ncu_rb)
     step ncu_rb 600 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 2 -c 1 -o gpurun_out/ncu_rb python tools/round_bench.py --cases 5x10 --lists 32 --skips 0 --iters 3
     ncu -i gpurun_out/ncu_rb.ncu-rep --page source --csv > gpurun_out/ncu_rb_source.csv 2>/dev/null
-    ncu -i gpurun_out/ncu_rb.ncu-rep --page raw --csv > gpurun_out/ncu_rb_raw.csv 2>/dev/null ;;
+    ncu -i gpurun_out/ncu_rb.ncu-rep --page raw --csv > gpurun_out/ncu_rb_raw.csv 2>/dev/null
+    rm -f gpurun_out/ncu_rb.ncu-rep ;;
 trace)
     for c in "1x1 64" "5x10 32" "5x10 64"; do set -- $c; tag=$(echo $1_$2)
       ATE_B200_LIB=$PWD/ate_replication_causalml_b200/libate_b200_trace.so ATE_ROUND_TRACE_OUT=gpurun_out/trace_$tag.csv step trace_$tag 300 python tools/round_bench.py --cases $1 --lists $2 --skips 0 --iters 2
@@ -41,10 +42,11 @@ trace)
 hbm)
     step hbm_passes 600 python tools/hbm_passes.py ;;
 ncu_hbm)
-    step ncu_hbm 900 ncu --set full --clock-control none --import-source on -k regex:'col_moments_kernel|col_apply|build_design|expand_col|aipw_score|bootstrap_kernel|gather_rows|cvdev|predict_rows|rk_rank|rk_hist|scatter_kernel|inner_key' -c 40 -o gpurun_out/ncu_hbm python tools/hbm_passes.py
-    ncu -i gpurun_out/ncu_hbm.ncu-rep --page raw --csv > gpurun_out/ncu_hbm_raw.csv 2>/dev/null ;;
+    step ncu_hbm 900 ncu --set full --clock-control none -k regex:'col_moments_kernel|col_apply|build_design|expand_col|aipw_score|bootstrap_kernel|gather_rows|cvdev|predict_rows|rk_rank|rk_hist|scatter_kernel|inner_key' -c 40 -o gpurun_out/ncu_hbm python tools/hbm_passes.py
+    ncu -i gpurun_out/ncu_hbm.ncu-rep --page raw --csv > gpurun_out/ncu_hbm_raw.csv 2>/dev/null
+    rm -f gpurun_out/ncu_hbm.ncu-rep ;;
 sass)
-    cuobjdump -sass ate_replication_causalml_b200/libate_b200.so > gpurun_out/libate_b200.sass 2>/dev/null ;;
+    python tools/sass_summary.py > gpurun_out/sass_summary.txt 2>&1 ;;
 smoke)
     step smoke 300 python -c "import __graft_entry__ as g; g.smoke()" ;;
 bench)
@@ -82,9 +84,21 @@ mgc4)
     step bench_c4_n$NG 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $NG --master-addr 127.0.0.1 --master-port 29514 bench.py --gpus $NG --workload C4 --steps 1 --warmup 1 --no-e2e
     grep -h '^{' gpurun_out/bench_c4_n$NG.log | tail -1 > gpurun_out/bench_c4_n$NG.json ;;
 ncu_round)
-    step ncu_round 900 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 150 -c 3 -o gpurun_out/ncu_round python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e ;;
+    step ncu_round 900 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 150 -c 3 -o gpurun_out/ncu_round python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e
+    ncu -i gpurun_out/ncu_round.ncu-rep --page raw --csv > gpurun_out/ncu_round_raw.csv 2>/dev/null
+    ncu -i gpurun_out/ncu_round.ncu-rep --page source --csv > gpurun_out/ncu_round_source.csv 2>/dev/null
+    rm -f gpurun_out/ncu_round.ncu-rep ;;
+ncu_wide)
+    step ncu_wide 600 ncu --set full --clock-control none --import-source on -k regex:irls_round_kernel -s 2 -c 1 -o gpurun_out/ncu_wide python tools/round_bench.py --cases 5x10 --lists ${WIDE_LIST:-128} --skips 0 --iters 3
+    ncu -i gpurun_out/ncu_wide.ncu-rep --page source --csv > gpurun_out/ncu_wide_source.csv 2>/dev/null
+    ncu -i gpurun_out/ncu_wide.ncu-rep --page raw --csv > gpurun_out/ncu_wide_raw.csv 2>/dev/null
+    rm -f gpurun_out/ncu_wide.ncu-rep ;;
 *)
     echo "unknown step $what" ;;
 esac
+done
+# gpurun merges at most 64 MiB back: drop the largest files until the directory fits
+while [ "$(du -sm gpurun_out | cut -f1)" -gt 56 ]; do
+    big=$(ls -S gpurun_out | head -1); echo "dropping gpurun_out/$big ($(du -sm gpurun_out/$big | cut -f1) MiB)"; rm -f "gpurun_out/$big"
 done
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,temperature.gpu,power.draw --format=csv,noheader
