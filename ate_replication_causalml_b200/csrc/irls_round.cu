@@ -178,15 +178,17 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
     static_assert(FMAX >= 1 && FMAX <= 4 && FMAX <= R_FMAX, "fits per CTA");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ DCta scta;
-    __shared__ int s_nk;
+    __shared__ int s_nnz[R_FMAX];
     const int ncols = a.ncols, pitch = ncols + R_PAD, stages = a.stages;
     const size_t stage_doubles = (size_t)ROWS * pitch;
     double *sx = reinterpret_cast<double *>(smem_raw);
     double *sv = sx + stage_doubles * stages;           // [stages][FMAX][ROWS]: v of every fit
     double *sr = sv + (size_t)stages * FMAX * ROWS;     // [stages][FMAX][ROWS]: r of every fit
-    double *sbeta = sr + (size_t)stages * FMAX * ROWS;  // [FMAX][ncols]: coefficients of every fit (zero beyond ni)
-    int *skk = reinterpret_cast<int *>(sbeta + (size_t)FMAX * ncols);  // the 4-column steps in which some coefficient is non-zero
-    uint64_t *full = reinterpret_cast<uint64_t *>(skk + ((ncols / 4 + 3) & ~1));
+    // the non-zero coefficients of every fit, compacted in ascending column order and padded to a multiple
+    // of four with (zero column, 0.0): eta is a sparse dot product over them
+    double *snzv = sr + (size_t)stages * FMAX * ROWS;                             // [FMAX][ncols] values
+    uint16_t *snzi = reinterpret_cast<uint16_t *>(snzv + (size_t)FMAX * ncols);   // [FMAX][ncols] columns
+    uint64_t *full = reinterpret_cast<uint64_t *>(snzi + (size_t)FMAX * ncols);  // (ncols % 8 == 0: aligned)
     uint64_t *vfull = full + stages, *empty = vfull + stages;
 
     // Hardware warp w runs on SM sub-partition w % 4.  With rolemap the roles are dealt so that the warps
@@ -210,10 +212,6 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
 
     for (int e = threadIdx.x; e < stages * ROWS * R_PAD; e += blockDim.x)
         sx[(size_t)(e / R_PAD) * pitch + ncols + (e % R_PAD)] = 0.0;  // the list's "zero column"
-    for (int e = threadIdx.x; e < FMAX * ncols; e += blockDim.x) {
-        const int f = e / ncols, c = e - f * ncols;
-        sbeta[e] = (f < nfit && c < a.ni) ? a.fits[scta.fit[f]].coef[c] : 0.0;
-    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(full + s, contiguous ? 1 : R_PWARPS);
@@ -223,23 +221,31 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         mbar_fence_init();
     }
     __syncthreads();
-    if (warp == 0) {
-        // the steps of four columns in which at least one fit has a non-zero coefficient: eta needs no others
-        int nk = 0;
-        const int nks = ncols >> 2;
-        for (int k0 = 0; k0 < nks; k0 += 32) {
-            const int kk = k0 + lane;
-            bool any = false;
-            if (kk < nks)
-#pragma unroll
-                for (int f = 0; f < FMAX; ++f)
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) any |= (sbeta[f * ncols + 4 * kk + c] != 0.0);
-            const unsigned m = __ballot_sync(0xffffffffu, any);
-            if (any) skk[nk + __popc(m & ((1u << lane) - 1u))] = kk;
-            nk += __popc(m);
+    if (hw_warp < FMAX) {
+        // warp f compacts the non-zero coefficients of fit f (a few dozen of ni on a lasso path)
+        const int f = hw_warp;
+        int nz = 0;
+        if (f < nfit && !(a.skip & 8)) {
+            const double *coef = a.fits[scta.fit[f]].coef;
+            for (int c0 = 0; c0 < a.ni; c0 += 32) {
+                const int c = c0 + lane;
+                const double bv = c < a.ni ? __ldg(coef + c) : 0.0;
+                const unsigned m = __ballot_sync(0xffffffffu, bv != 0.0);
+                if (bv != 0.0) {
+                    const int at = nz + __popc(m & ((1u << lane) - 1u));
+                    snzv[(size_t)f * ncols + at] = bv;
+                    snzi[(size_t)f * ncols + at] = (uint16_t)c;
+                }
+                nz += __popc(m);
+            }
+            const int nzp = (nz + 3) & ~3;
+            if (lane < nzp - nz) {
+                snzv[(size_t)f * ncols + nz + lane] = 0.0;
+                snzi[(size_t)f * ncols + nz + lane] = (uint16_t)ncols;  // the staged rows' zero column
+            }
+            nz = nzp;
         }
-        if (lane == 0) s_nk = nk;
+        if (lane == 0) s_nnz[f] = nz;
     }
     __syncthreads();
     // Ring protocol: every consumer warp visits every slot in order and arrives on `empty` for it,
@@ -311,12 +317,15 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         }
     } else if (warp >= R_EVAL) {
         // ------------------------------ evaluation ------------------------------
-        // eta of eight rows for every fit of the CTA is one 8 x 8 DMMA accumulation: A = the eight staged
-        // rows, four consecutive columns per step (conflict-light loads, the same for all fits), B = the
-        // fits' coefficients in shared memory.  Only the steps in which some coefficient is non-zero are
-        // taken (a few dozen of ncols / 4 on a lasso path).  One shuffle then hands lane (row g, k4) the eta
-        // of fit k4, and exp / divide / log run once per lane whatever the number of fits.
-        // v and r are published (and the slot released) BEFORE the log of the deviance is taken.
+        // eta = a0 + x . beta is a SPARSE dot product over the fit's non-zero coefficients (a few dozen of ni
+        // on a lasso path) on the FMA pipe: as an 8 x 8 DMMA accumulation (eight rows x eight fits) it took
+        // 21-31 % of the DMMA pipe, which the Gram needs, for at most half-used tiles.  A quad of lanes owns a
+        // row; a fit's entries form four interleaved subsets (t mod 4) summed as (s0 + s1) + (s2 + s3)
+        // whatever the number of fits, so a fit's eta does not depend on which fits share its CTA: with
+        // three or four fits a lane sums all four subsets of its fit, with two fits two lanes share a fit,
+        // with one fit the four lanes take one subset each.  Lane (row g, k4) then holds fit k4, and exp /
+        // divide / log run once per lane.  v and r are published (and the slot released) BEFORE the log of
+        // the deviance is taken.
         const int e = warp - R_EVAL;
         const int ni = a.ni;
         const int grp = e % EWPS, turn = e / EWPS;
@@ -337,10 +346,12 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
         }
         double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0;
         const int r0 = 8 * grp, rr = r0 + g;
-        const int nk = (a.skip & 8) ? 0 : s_nk;
-        const bool bok = g < FMAX;
-        const double *brow = sbeta + (size_t)(bok ? g : 0) * ncols + k4;
-        const int src_lane = (lane & ~3) | (k4 >> 1);
+        // this lane's share of the dot products: fit dfit, subsets [sub0, sub0 + nsub)
+        const int dfit = nfit >= 3 ? k4 : nfit == 2 ? (k4 & 1) : 0;
+        const int sub0 = nfit >= 3 ? 0 : nfit == 2 ? 2 * (k4 >> 1) : k4;
+        const int nnz = (dfit < nfit && dfit < FMAX) ? s_nnz[dfit] : 0;
+        const double *nzv = snzv + (size_t)(dfit < FMAX ? dfit : 0) * ncols + sub0;
+        const uint16_t *nzi = snzi + (size_t)(dfit < FMAX ? dfit : 0) * ncols + sub0;
         for (int it = 0; it < nit; ++it) {
             const int s = it % stages;
             const uint32_t ph = (uint32_t)(it / stages) & 1u;
@@ -351,34 +362,41 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             }
             RTRACE(1 + (grp & 1), it);  // eval warp of group 0 / 1: rows landed
             const double *slot = sx + stage_doubles * s;
-            const double *arow = slot + (size_t)rr * pitch + k4;
-            double c0 = 0.0, c1 = 0.0, d0 = 0.0, d1 = 0.0;  // two accumulation chains
-            int j = 0;
-            for (; j + 7 < nk; j += 8) {  // eight steps at a time: their operand loads overlap
-                int kq[8];
-                double aq[8], bq[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u) kq[u] = skk[j + u] << 2;
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    aq[u] = arow[kq[u]];
-                    bq[u] = bok ? brow[kq[u]] : 0.0;
+            const double *xrow = slot + (size_t)rr * pitch;
+            double dot;
+            if (nfit >= 3) {
+                double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll 2
+                for (int t = 0; t < nnz; t += 4) {
+                    const ushort4 ci = *reinterpret_cast<const ushort4 *>(nzi + t);
+                    const double2 b01 = *reinterpret_cast<const double2 *>(nzv + t), b23 = *reinterpret_cast<const double2 *>(nzv + t + 2);
+                    s0 = fma(xrow[ci.x], b01.x, s0);
+                    s1 = fma(xrow[ci.y], b01.y, s1);
+                    s2 = fma(xrow[ci.z], b23.x, s2);
+                    s3 = fma(xrow[ci.w], b23.y, s3);
                 }
-#pragma unroll
-                for (int u = 0; u < 8; u += 2) {
-                    dmma884(c0, c1, aq[u], bq[u]);
-                    dmma884(d0, d1, aq[u + 1], bq[u + 1]);
+                dot = (s0 + s1) + (s2 + s3);
+            } else if (nfit == 2) {
+                double sa = 0.0, sb = 0.0;
+#pragma unroll 2
+                for (int t = 0; t < nnz; t += 4) {
+                    const ushort2 ci = *reinterpret_cast<const ushort2 *>(nzi + t);
+                    const double2 bb = *reinterpret_cast<const double2 *>(nzv + t);
+                    sa = fma(xrow[ci.x], bb.x, sa);
+                    sb = fma(xrow[ci.y], bb.y, sb);
                 }
+                const double part = sa + sb;  // (s0 + s1) on lanes k4 < 2, (s2 + s3) on the others
+                const double lo = __shfl_sync(0xffffffffu, part, (lane & ~3) | (k4 & 1));
+                const double hi = __shfl_sync(0xffffffffu, part, (lane & ~3) | (k4 & 1) | 2);
+                dot = lo + hi;
+            } else {
+                double sa = 0.0;
+#pragma unroll 4
+                for (int t = 0; t < nnz; t += 4) sa = fma(xrow[nzi[t]], nzv[t], sa);
+                const double s01 = sa + __shfl_xor_sync(0xffffffffu, sa, 1);  // s0 + s1 | s2 + s3 (commutative: same bits on both lanes)
+                const double oth = __shfl_xor_sync(0xffffffffu, s01, 2);
+                dot = k4 < 2 ? s01 + oth : oth + s01;                         // (s0 + s1) + (s2 + s3)
             }
-            for (; j < nk; ++j) {
-                const int ka = skk[j] << 2;
-                dmma884(c0, c1, arow[ka], bok ? brow[ka] : 0.0);
-            }
-            c0 += d0;
-            c1 += d1;
-            // lane (g, k4) holds fits 2 k4 and 2 k4 + 1 of row g; hand fit k4 to lane (g, k4)
-            const double v0 = __shfl_sync(0xffffffffu, c0, src_lane), v1 = __shfl_sync(0xffffffffu, c1, src_lane);
-            const double dot = (k4 & 1) ? v1 : v0;
             const long long t = c_begin + (long long)it * ROWS + rr;
             const bool valid = mine && t < c_end && !(t >= hb && t < he);
             const double yi = slot[(size_t)rr * pitch + a.iy];
@@ -891,7 +909,7 @@ extern "C" int ate_round_plan_describe(int nfit, const int *list_cols, int stage
 // slot geometry for a staged width: 32-row slots while three of them fit, else 16-row slots
 // fixed shared memory beside the ring: the fits' coefficients, the list of non-zero column steps, slack
 static size_t round_fixed_smem(int ncs, int fmax) {
-    return sizeof(double) * (size_t)fmax * ncs + sizeof(int) * (size_t)(ncs / 4 + 4) + 2048;
+    return (sizeof(double) + sizeof(uint16_t)) * (size_t)fmax * ncs + 64 + 2048;  // non-zero lists; barriers and slack
 }
 static int round_rows_for(int ncs, int fmax) {
     static const int forced = getenv("ATE_ROUND_ROWS") ? atoi(getenv("ATE_ROUND_ROWS")) : 0;  // A/B measurements
