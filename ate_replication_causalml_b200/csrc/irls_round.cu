@@ -152,14 +152,15 @@ __device__ __forceinline__ void mma_half_slot(double (&accA)[4][2], double (&acc
     for (int kk = 0; kk < ROWS / 4; ++kk) {
         const char *rowp = sbase + (size_t)kk * kstep_bytes;  // (warp-uniform)
         const double vv = vs[kk * 4];
+        // v scales the A operand (one or two products per k-step) rather than the NA B operands
         double fb[NA];
 #pragma unroll
-        for (int n = 0; n < NA; ++n) fb[n] = *reinterpret_cast<const double *>(rowp + offB[n]) * vv;
-        const double fa = *reinterpret_cast<const double *>(rowp + offA0);
+        for (int n = 0; n < NA; ++n) fb[n] = *reinterpret_cast<const double *>(rowp + offB[n]);
+        const double fa = *reinterpret_cast<const double *>(rowp + offA0) * vv;
 #pragma unroll
         for (int n = 0; n < NA; ++n) dmma884(accA[n][0], accA[n][1], fa, fb[n]);
         if (NB > 0) {
-            const double fa1 = *reinterpret_cast<const double *>(rowp + offA1);
+            const double fa1 = *reinterpret_cast<const double *>(rowp + offA1) * vv;
 #pragma unroll
             for (int n = 0; n < NB; ++n) dmma884(accB[n][0], accB[n][1], fa1, fb[n]);
         }
@@ -344,7 +345,8 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             he = ft.hole_begin + ft.hole_len;
             lead = scta.lead[fsel] != 0;
         }
-        double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0;
+        double s_xmz = 0.0, s_sr = 0.0, s_dev = 0.0, lik = 1.0;
+        int nlik = 0;
         const int r0 = 8 * grp, rr = r0 + g;
         // this lane's share of the dot products: fit dfit, subsets [sub0, sub0 + nsub)
         const int dfit = nfit >= 3 ? k4 : nfit == 2 ? (k4 & 1) : 0;
@@ -422,24 +424,30 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
                 mbar_arrive(empty + s);  // ... and this warp is done with its staged rows
             }
             if (!(a.skip & 4)) {
-                // log-likelihood term, off the slot's critical path.  y is 0/1 on this path, so one of the
-                // two log terms vanishes: ONE log per lane, evaluated by all lanes together; a non-binary
-                // response takes the general form
+                // log-likelihood term, off the slot's critical path.  y is 0/1 on this path, so the term of a row
+                // is log(y ? q : 1 - q): the lane multiplies these probabilities up (each >= pmin = 1e-5, so
+                // sixteen of them stay above 1e-80) and takes ONE log per sixteen slots -- the log was a fifth of
+                // the eval warps' chain.  A non-binary response takes the general form row by row.
                 const double qc = fmin(fmax(q, pmin), 1.0 - pmin);
                 const bool count = lead && valid;
                 const bool binary = (yi == 0.0 || yi == 1.0);
-                double ll;
-                if (__all_sync(0xffffffffu, binary || !count))
-                    ll = log(yi == 1.0 ? qc : 1.0 - qc);
-                else
-                    ll = yi * log(qc) + (1.0 - yi) * log(1.0 - qc);
+                if (__all_sync(0xffffffffu, binary || !count)) {
+                    lik *= count ? (yi == 1.0 ? qc : 1.0 - qc) : 1.0;
+                    if (++nlik == 16) {
+                        s_dev -= w * log(lik);
+                        lik = 1.0;
+                        nlik = 0;
+                    }
+                } else if (count) {
+                    s_dev -= w * (yi * log(qc) + (1.0 - yi) * log(1.0 - qc));
+                }
                 if (count) {
                     s_xmz += vi;
                     s_sr += ri;
-                    s_dev -= w * ll;
                 }
             }
         }
+        s_dev -= w * log(lik);
         // lanes with the same k4 hold partial sums of the same fit
 #pragma unroll
         for (int o = 16; o >= 4; o >>= 1) {
@@ -802,13 +810,21 @@ int build_groups(int P, const std::vector<int> &prob_of, const std::vector<int> 
             hv.clear();
             make_halves(0, ntr, hv);
             if ((int)hv.size() > cap) {
-                for (size_t b0 = 0; b0 < hv.size(); b0 += cap) {
-                    Group g;
-                    g.prob = p; g.nfit = 1; g.fit[0] = f; g.lead[0] = (b0 == 0);
-                    for (size_t b = b0; b < hv.size() && b < b0 + cap; ++b) {
-                        g.halves.push_back(hv[b]);
-                        g.tiles += hv[b].load;
-                    }
+                // the CTAs of a split list all stage and evaluate the rows, so they should finish together:
+                // the halves are dealt heaviest first, back and forth, to equally many per CTA
+                const int ng = ((int)hv.size() + cap - 1) / cap;
+                std::vector<Half> sorted = hv;
+                std::stable_sort(sorted.begin(), sorted.end(), [](const Half &x, const Half &y) { return x.load > y.load; });
+                std::vector<Group> parts(ng);
+                for (size_t b = 0; b < sorted.size(); ++b) {
+                    const int lap = (int)(b / ng), pos = (int)(b % ng);
+                    Group &g = parts[(lap & 1) ? ng - 1 - pos : pos];
+                    g.halves.push_back(sorted[b]);
+                    g.tiles += sorted[b].load;
+                }
+                for (int q = 0; q < ng; ++q) {
+                    Group &g = parts[q];
+                    g.prob = p; g.nfit = 1; g.fit[0] = f; g.lead[0] = (q == 0);
                     deal_halves(g);
                     groups.push_back(g);
                 }
