@@ -145,10 +145,14 @@ __device__ long long g_rtrace[TR_SLOTS * TR_EVENTS + 8];
 // DMMAs: a run-time tile count inside the loop costs a jump table and a WARPSYNC per tile row and
 // k-step (measured: more than half of the MMA warps' issue slots).  sbase: the slot's rows (shared
 // memory, bytes); the operand offsets are per-lane byte offsets into a row, row k4 of each k-step.
+#ifndef ATE_MMA_UNROLL
+#define ATE_MMA_UNROLL 2
+#endif
+constexpr int MMA_UNROLL = ATE_MMA_UNROLL;  // k-steps per trip of the loop below (A/B builds: tools/build_variant_lib.sh)
 template <int NA, int NB, int ROWS>
 __device__ __forceinline__ void mma_half_slot(double (&accA)[4][2], double (&accB)[4][2], const char *sbase, uint32_t kstep_bytes,
                                               const double *vs, uint32_t offA0, uint32_t offA1, const uint32_t (&offB)[4]) {
-#pragma unroll 2
+#pragma unroll(MMA_UNROLL)
     for (int kk = 0; kk < ROWS / 4; ++kk) {
         const char *rowp = sbase + (size_t)kk * kstep_bytes;  // (warp-uniform)
         const double vv = vs[kk * 4];
@@ -937,9 +941,13 @@ static int round_rows_for(int ncs, int fmax) {
 // step but a fit's first); one on first steps and for wider rows (FMA-pipe helpers)
 static int round_fmax(int ncs, int init) { return ((ncs + 63) / 64 <= 5 && !init) ? R_FMAX : 1; }
 
-int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std::vector<RoundProblem> &probs,
+int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, const std::vector<RoundProblem> &probs,
                      const std::vector<RoundFit> &fits, std::vector<RoundSlot> &slots, double **packed,
                      long long *packed_count, RoundStats *stats) {
+    // two launches of one round (fits on their first step beside fits under way) must not share result,
+    // partial or descriptor buffers: every cached buffer exists once per bank
+    const char *const nm_packed = bank ? "round.packed.1" : "round.packed", *const nm_part = bank ? "round.partials.1" : "round.partials",
+               *const nm_hdesc = bank ? "round.hdesc.1" : "round.hdesc", *const nm_ddesc = bank ? "round.ddesc.1" : "round.ddesc";
     const int nfits = (int)fits.size(), P = (int)probs.size();
     if (ncs % 8 != 0 || ncs <= ni - 1 || iy >= ncs || ni < 1) return ate_fail(ctx, -1, "irls_round: bad staged width %d", ncs);
     const int it_e = (ncs + 63) / 64;
@@ -1028,8 +1036,8 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
         part_doubles += ((size_t)eplen * fit_chunks[f] + 3) / 4 * 4;  // the next fit's tiles are stored 16 bytes at a time
     }
     void *dpacked = nullptr, *dpart = nullptr;
-    ATE_TRY(ate_cached(ctx, "round.packed", sizeof(double) * (size_t)std::max(pk, 1LL), &dpacked));
-    ATE_TRY(ate_cached(ctx, "round.partials", sizeof(double) * std::max(part_doubles, (size_t)1), &dpart));
+    ATE_TRY(ate_cached(ctx, nm_packed, sizeof(double) * (size_t)std::max(pk, 1LL), &dpacked));
+    ATE_TRY(ate_cached(ctx, nm_part, sizeof(double) * std::max(part_doubles, (size_t)1), &dpart));
     *packed = (double *)dpacked;
     *packed_count = pk;
 
@@ -1042,8 +1050,8 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std:
     const size_t o_fits = up16(b_probs), o_ctas = o_fits + up16(b_fits), o_folds = o_ctas + up16(b_ctas),
                  total = o_folds + up16(b_folds);
     void *hst = nullptr, *ddesc = nullptr;
-    ATE_TRY(ate_cached_pinned(ctx, "round.hdesc", total, &hst));
-    ATE_TRY(ate_cached(ctx, "round.ddesc", total, &ddesc));
+    ATE_TRY(ate_cached_pinned(ctx, nm_hdesc, total, &hst));
+    ATE_TRY(ate_cached(ctx, nm_ddesc, total, &ddesc));
     memset(hst, 0, total);
     DProb *hp = (DProb *)hst;
     DFit *hf = (DFit *)((char *)hst + o_fits);
@@ -1243,13 +1251,13 @@ extern "C" int ate_round_kernel_bench(ate_ctx *ctx, long long nrows, int ni, int
     long long count = 0;
     RoundStats st;
     ctx->debug_skip = skip_mask;
-    int rc = ate_i_irls_round(ctx, ncs, ni, iy, 0, probs, fits, slots, &packed, &count, &st);  // warm-up
+    int rc = ate_i_irls_round(ctx, ncs, ni, iy, 0, 0, probs, fits, slots, &packed, &count, &st);  // warm-up
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     float ms = 0.f;
     if (rc == 0 && cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess) {
         cudaStreamSynchronize(ctx->stream);
         cudaEventRecord(e0, ctx->stream);
-        for (int it = 0; it < iters && rc == 0; ++it) rc = ate_i_irls_round(ctx, ncs, ni, iy, 0, probs, fits, slots, &packed, &count, &st);
+        for (int it = 0; it < iters && rc == 0; ++it) rc = ate_i_irls_round(ctx, ncs, ni, iy, 0, 0, probs, fits, slots, &packed, &count, &st);
         cudaEventRecord(e1, ctx->stream);
         if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = ate_fail(ctx, -100, "ate_round_kernel_bench: %s", cudaGetErrorString(cudaGetLastError()));
         cudaEventElapsedTime(&ms, e0, e1);

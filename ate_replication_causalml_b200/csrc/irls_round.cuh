@@ -46,6 +46,8 @@ struct RoundStats {
 // the step kernel and the fold kernel.  `packed` (device, grow-only, owned by the ctx cache) receives,
 // for every live fit, its sums and its Gram at slots[fit]; *packed_count = doubles in use (what a
 // multi-GPU driver all-reduces).  ncs: columns staged per row (multiple of 8 covering [0, ni) and iy).
-int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, const std::vector<RoundProblem> &probs,
+// bank (0 / 1): which set of cached buffers the call uses -- two calls whose results are alive at the
+// same time (the two launches of one round) take different banks.
+int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, const std::vector<RoundProblem> &probs,
                      const std::vector<RoundFit> &fits, std::vector<RoundSlot> &slots, double **packed,
                      long long *packed_count, RoundStats *stats);

@@ -52,7 +52,9 @@ struct LognetFit {
     const double *vp;
     double flmin;
     const double *ulam;
-    const int *nlam_ptr;
+    const int *nlam_ptr;  // user lambdas: how many; a cv-fold fit: its full-data fit's lmu so far
+    const int *lead_done; // a cv-fold fit: its full-data fit's SI_DONE (nlam_ptr is final only then); else NULL
+    double *seq;          // a full-data fit: the lambda sequence its cv-fold fits follow (their ulam)
     int nlam;
     double thr;
     int maxit;
@@ -69,8 +71,15 @@ constexpr int CD_THREADS = 256;
 struct RoundDev {
     const double *sums;  // X^T r [ni], X^T v [ni], sum v x^2 [ni], then XMZ, SR, DEV
     double *H;           // ldh x ldh over the column list of the round
-    int ldh, pad;
+    int ldh, live;       // live = 0: the fit takes no part in this round
 };
+// lambdas a fit may run: all of its own sequence, or, for a cv-fold fit, those its full-data fit reached
+// (known once that fit is done; until then the fold fit simply continues)
+__device__ __forceinline__ int fit_nlam(const LognetFit &f) {
+    if (f.flmin < 1.0) return f.nlam;
+    if (f.lead_done && !*f.lead_done) return f.nlam;
+    return min(f.nlam, *f.nlam_ptr);
+}
 __device__ __forceinline__ int *fit_slist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni; }
 __device__ __forceinline__ int *fit_glist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + f.ldh; }
 __device__ __forceinline__ int *fit_scal_i(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + 2 * (size_t)f.ldh; }
@@ -177,8 +186,16 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
-    if (si[SI_DONE]) {
+    if (si[SI_DONE] || !rd.live) {
         if (tid == 0) si[SI_SOLVE] = 0;
+        return;
+    }
+    if (f.lead_done && *f.lead_done && si[SI_ILM] >= *f.nlam_ptr && si[SI_PHASE] != PH_INIT) {
+        // a cv-fold fit that ran ahead of its full-data fit, which has now stopped short of this lambda
+        if (tid == 0) {
+            si[SI_DONE] = 1;
+            si[SI_SOLVE] = 0;
+        }
         return;
     }
     if (si[SI_RETRY]) {  // the bookkeeping of this step was done last round; H now covers the strong set
@@ -201,7 +218,7 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
     const int phase = si[SI_PHASE];
     const double b0 = sd[SD_B0];
     double al = sd[SD_AL], al0 = sd[SD_AL0];
-    const int nlam = (f.flmin < 1.0) ? f.nlam : min(f.nlam, *f.nlam_ptr);
+    const int nlam = fit_nlam(f);
     const int mnl = min(GLM_MNLAM, nlam);
     double dev0 = sd[SD_DEV0], dev1 = sd[SD_DEV1], shr = sd[SD_SHR], alf = sd[SD_ALF];
 
@@ -300,6 +317,19 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
                 f.alm[ilm] = al;
                 f.dev[ilm] = devr;
                 si[SI_LMU] = ilm + 1;
+                if (f.seq && f.flmin < 1.0 && ilm == 2) {
+                    // Three lambdas are recorded: the whole sequence is now determined (lambda_k =
+                    // lambda_{k-1} alf, the products this fit itself will form; lambda_1 by R's fix.lam
+                    // extrapolation), so the cv-fold fits may start while this fit is still running.
+                    const double l1 = f.alm[1];
+                    f.seq[0] = exp(2.0 * log(l1) - log(al));
+                    f.seq[1] = l1;
+                    double a = al;
+                    for (int k = 2; k < f.nlam; ++k) {
+                        f.seq[k] = a;
+                        a *= alf;
+                    }
+                }
             }
             bool stop = stop_path;
             if (!stop && ilm + 1 >= mnl && f.flmin < 1.0) {
@@ -362,6 +392,8 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
             // fix.lam: lambda[1] was `big`; R rewrites it by log-linear extrapolation before the
             // sequence is handed to the CV folds
             if (f.flmin < 1.0 && si[SI_LMU] > 2) f.alm[0] = exp(2.0 * log(f.alm[1]) - log(f.alm[2]));
+            if (f.seq)
+                for (int k = 0; k < si[SI_LMU]; ++k) f.seq[k] = f.alm[k];
         }
     }
 }
@@ -370,7 +402,7 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
 // H holds X_L^T V X_L over the column list L the step used (positions gpos).  At the end the list for
 // the next step is rebuilt: the strong set plus every column whose gradient is within 10 % of the
 // next strong-rule / KKT threshold, ordered so that the MMA warps' gathered operand loads spread over
-// the shared-memory banks.  flags_out[2 fit + {0, 1}] = {done, length of the next list}.
+// the shared-memory banks.  flags_out[3 fit + {0, 1, 2}] = {done, length of the next list, lambdas recorded}.
 __global__ void __launch_bounds__(CD_THREADS)
 lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev, int *__restrict__ flags_out) {
     const LognetFit f = fits[blockIdx.x];
@@ -378,10 +410,11 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x, ldh = rd.ldh;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
-    if (si[SI_DONE] || !si[SI_SOLVE]) {
+    if (si[SI_DONE] || !si[SI_SOLVE] || !rd.live) {
         if (tid == 0) {
-            flags_out[2 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
-            flags_out[2 * blockIdx.x + 1] = si[SI_DONE] ? 0 : si[SI_NG];
+            flags_out[3 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
+            flags_out[3 * blockIdx.x + 1] = si[SI_DONE] ? 0 : si[SI_NG];
+            flags_out[3 * blockIdx.x + 2] = si[SI_LMU];
         }
         return;
     }
@@ -545,7 +578,7 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
     //      non-strong column is still the gradient this round started from. ----
     double tnext;
     {
-        const int nlam = (f.flmin < 1.0) ? f.nlam : min(f.nlam, *f.nlam_ptr);
+        const int nlam = fit_nlam(f);
         const double alf = sd[SD_ALF];
         double aln;
         if (f.flmin >= 1.0)
@@ -592,7 +625,7 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
         const int npad = (nG + 31) / 32 * 32;
         for (int c = nG; c < npad && c < f.ldh; ++c) glist[c] = f.ncs;
         si[SI_NG] = nG;
-        flags_out[2 * blockIdx.x + 1] = nG;
+        flags_out[3 * blockIdx.x + 1] = nG;
         if (!retry) {
             f.coef[ni] = b0 - dotbm;
             sd[SD_B0] = b0;
@@ -604,7 +637,8 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
                 si[SI_DONE] = 1;
             }
         }
-        flags_out[2 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
+        flags_out[3 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
+        flags_out[3 * blockIdx.x + 2] = si[SI_LMU];
     }
 }
 
@@ -787,7 +821,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
 
     // ---- device state: one cached block, carved ----
     Carver cv;
-    double *dcoef, *dstd, *dout, *dvp, *dulam, *dysum, *dpart, *dcv;
+    double *dcoef, *dstd, *dout, *dvp, *dulam, *dysum, *dpart, *dcv, *dseq;
     int *dsti, *dflags, *dnl;
     LognetFit *dfits;
     RoundDev *drdev;
@@ -799,11 +833,12 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         dout = cv.take<double>(out_len * nfits);
         dvp = cv.take<double>(ni);
         dulam = cv.take<double>(nlam);
+        dseq = cv.take<double>((size_t)nlam * nlead);
         dysum = cv.take<double>((size_t)P * nsegp);
         dpart = cv.take<double>((size_t)ev_blocks * nlam);
         dcv = cv.take<double>((size_t)(nfol > 0 ? nfol : 1) * nlam);
         dsti = cv.take<int>(si_len * nfits);
-        dflags = cv.take<int>(2 * (size_t)nfits);
+        dflags = cv.take<int>(3 * (size_t)nfits);
         dnl = cv.take<int>(1);
         dfits = cv.take<LognetFit>(nfits);
         drdev = cv.take<RoundDev>(nfits);
@@ -815,7 +850,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         }
     }
     ATE_CUDA(ctx, cudaMemsetAsync(dout, 0, sizeof(double) * out_len * nfits, ctx->stream));
-    ATE_CUDA(ctx, cudaMemsetAsync(dflags, 0, sizeof(int) * 2 * nfits, ctx->stream));
+    ATE_CUDA(ctx, cudaMemsetAsync(dflags, 0, sizeof(int) * 3 * nfits, ctx->stream));
     if (vp_host) ATE_CUDA(ctx, cudaMemcpyAsync(dvp, vp_host, sizeof(double) * ni, cudaMemcpyHostToDevice, ctx->stream));
     if (po.flmin >= 1.0) {
         ATE_CUDA(ctx, cudaMemcpyAsync(dulam, po.ulam, sizeof(double) * nlam, cudaMemcpyHostToDevice, ctx->stream));
@@ -882,10 +917,14 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             g.flmin = po.flmin;
             g.ulam = po.flmin >= 1.0 ? dulam : nullptr;
             g.nlam_ptr = po.flmin >= 1.0 ? dnl : nullptr;
+            g.lead_done = nullptr;
+            g.seq = dseq + (size_t)nlam * id;
         } else {
             g.flmin = 1.0;
-            g.ulam = hf[p].alm;
+            g.ulam = hf[p].seq;
             g.nlam_ptr = hf[p].st_i + si_scal + SI_LMU;
+            g.lead_done = hf[p].st_i + si_scal + SI_DONE;
+            g.seq = nullptr;
         }
         if (g.nt < 2.0) return ate_fail(ctx, -1, "cv_binomial: a fit with %g observations", g.nt);
     }
@@ -919,9 +958,9 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     auto tnow = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     double t_host = 0.0, t_wait = 0.0, t_mark = tnow();
 
-    std::vector<int> hdone(nfits, 0), hng(nfits, 0);
+    std::vector<int> hdone(nfits, 0), hng(nfits, 0), hlmu(nfits, 0), age(nfits, -1);
     void *hflags_v = nullptr, *hrdev_v = nullptr;
-    ATE_TRY(ate_cached_pinned(ctx, "binom.hflags", sizeof(int) * 2 * (size_t)nfits, &hflags_v));
+    ATE_TRY(ate_cached_pinned(ctx, "binom.hflags", sizeof(int) * 3 * (size_t)nfits, &hflags_v));
     ATE_TRY(ate_cached_pinned(ctx, "binom.hrdev", sizeof(RoundDev) * (size_t)nfits, &hrdev_v));
     int *hflags = (int *)hflags_v;
     RoundDev *hrdev = (RoundDev *)hrdev_v;
@@ -930,60 +969,88 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     int rounds = 0;
     const int max_rounds = nlam * 60 + 100;
     RoundStats rst;
-    // two lock-step phases: the full-data fits fix the lambda sequences, then all CV folds.  One
-    // round = step kernel for every live fit (evaluation + Gram over the predicted lists) -> (ranks
-    // sharing the fit: all-reduce of the packed results) -> bookkeeping -> coordinate-descent solve.
-    for (int phase = 0; phase < 2; ++phase) {
-        const int lo = phase == 0 ? 0 : nlead, hi = phase == 0 ? nlead : nfits;
-        if (lo == hi) continue;
-        for (int round_in_phase = 0;; ++round_in_phase) {
-            int live = 0;
-            for (int id = 0; id < nfits; ++id) {
-                RoundFit &r = rfits[id];
-                r.live = (id >= lo && id < hi && !hdone[id]) ? 1 : 0;
-                if (!r.live) continue;
-                ++live;
-                r.prob = hf[id].prob;
-                r.hole_begin = hf[id].hole_begin;
-                r.hole_len = hf[id].hole_len;
-                r.w = 1.0 / fit_nt[id];
-                r.coef = hf[id].coef;
-                r.colidx = hf[id].st_i + 6 * (size_t)ni + ldh;  // the list the last solve left
-                r.nG = hng[id];
+    // Lock-step rounds over ALL fits.  One round = step kernel for every live fit (evaluation + Gram over
+    // the predicted lists) -> (ranks sharing the fit: all-reduce of the packed results) -> bookkeeping ->
+    // coordinate-descent solve.  The full-data fit of a problem fixes the lambda sequence of its cv-fold
+    // fits; the sequence is determined once three lambdas are recorded (lognet_pre_kernel publishes it
+    // then), so the fold fits join a few rounds behind and share the CTAs of their full-data fit instead
+    // of waiting for it to finish.  ATE_TWO_PHASE=1: the fold fits start when the full-data fit is done.
+    static const bool two_phase = getenv("ATE_TWO_PHASE") && getenv("ATE_TWO_PHASE")[0] == '1';
+    for (;;) {
+        int live = 0, starting = 0;
+        for (int id = 0; id < nfits; ++id) {
+            RoundFit &r = rfits[id];
+            r.live = 0;
+            if (hdone[id]) continue;
+            if (age[id] < 0) {  // not started yet
+                bool go = id < nlead;
+                if (!go) {
+                    const int p = hf[id].prob;
+                    go = hdone[p] || (!two_phase && (po.flmin >= 1.0 || hlmu[p] >= 3));
+                }
+                if (!go) continue;
+                age[id] = 0;
             }
-            if (!live) break;
+            r.live = 1;
+            ++live;
+            starting += (age[id] == 0);
+            r.prob = hf[id].prob;
+            r.hole_begin = hf[id].hole_begin;
+            r.hole_len = hf[id].hole_len;
+            r.w = 1.0 / fit_nt[id];
+            r.coef = hf[id].coef;
+            r.colidx = hf[id].st_i + 6 * (size_t)ni + ldh;  // the list the last solve left
+            r.nG = hng[id];
+        }
+        if (!live) break;
+        // the first step of a fit also needs sum v x^2 of every column: a launch of its own (other template
+        // instantiation, other result bank) beside the launch of the fits that are under way
+        for (int bank = 0; bank < 2; ++bank) {
+            const int want_init = bank;  // bank 0: fits under way, bank 1: fits on their first step
+            if ((want_init ? starting : live - starting) == 0) continue;
+            std::vector<RoundFit> sel = rfits;
+            for (int id = 0; id < nfits; ++id)
+                if (sel[id].live && (age[id] == 0) != (want_init != 0)) sel[id].live = 0;
             double *packed = nullptr;
             long long count = 0;
-            ATE_TRY(ate_i_irls_round(ctx, ncs, ni, iy, round_in_phase == 0 ? 1 : 0, rprobs, rfits, slots, &packed, &count, &rst));
-            for (int id = lo; id < hi; ++id) {
+            ATE_TRY(ate_i_irls_round(ctx, ncs, ni, iy, want_init, bank, rprobs, sel, slots, &packed, &count, &rst));
+            for (int id = 0; id < nfits; ++id) {
+                if (!sel[id].live) continue;
                 hrdev[id].sums = packed + slots[id].sums_off;
                 hrdev[id].H = packed + slots[id].H_off;
                 hrdev[id].ldh = slots[id].ldh;
-                hrdev[id].pad = 0;
             }
-            ATE_CUDA(ctx, cudaMemcpyAsync(drdev + lo, hrdev + lo, sizeof(RoundDev) * (hi - lo), cudaMemcpyHostToDevice, ctx->stream));
             if (sharded && count > 0) ATE_TRY(ate_i_allreduce(ctx, packed, count));
-            lognet_pre_kernel<<<hi - lo, CD_THREADS, pre_smem, ctx->stream>>>(dfits + lo, drdev + lo);
-            ATE_LAUNCHED(ctx);
-            lognet_solve_kernel<<<hi - lo, CD_THREADS, cd_smem, ctx->stream>>>(dfits + lo, drdev + lo, dflags + 2 * (size_t)lo);
-            ATE_LAUNCHED(ctx);
-            ATE_CUDA(ctx, cudaMemcpyAsync(hflags + 2 * (size_t)lo, dflags + 2 * (size_t)lo, sizeof(int) * 2 * (hi - lo),
-                                          cudaMemcpyDeviceToHost, ctx->stream));
-            if (timing) { const double t = tnow(); t_host += t - t_mark; t_mark = t; }
-            ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-            if (timing) { const double t = tnow(); t_wait += t - t_mark; t_mark = t; }
-            for (int id = lo; id < hi; ++id) {
-                if (hdone[id]) continue;
-                hdone[id] = hflags[2 * (size_t)id];
-                hng[id] = hflags[2 * (size_t)id + 1];
-            }
             if (stats) {
                 stats->step_launches += 1;
                 stats->row_fits += (double)rst.row_fits;
                 stats->rows_staged += (double)rst.rows_staged;
             }
-            if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
         }
+        for (int id = 0; id < nfits; ++id) hrdev[id].live = rfits[id].live;
+        ATE_CUDA(ctx, cudaMemcpyAsync(drdev, hrdev, sizeof(RoundDev) * nfits, cudaMemcpyHostToDevice, ctx->stream));
+        // the full-data fits first: what they record this round (lmu, done, the sequence) is what their
+        // fold fits read in the second launch
+        lognet_pre_kernel<<<nlead, CD_THREADS, pre_smem, ctx->stream>>>(dfits, drdev);
+        ATE_LAUNCHED(ctx);
+        if (nfol > 0) {
+            lognet_pre_kernel<<<nfol, CD_THREADS, pre_smem, ctx->stream>>>(dfits + nlead, drdev + nlead);
+            ATE_LAUNCHED(ctx);
+        }
+        lognet_solve_kernel<<<nfits, CD_THREADS, cd_smem, ctx->stream>>>(dfits, drdev, dflags);
+        ATE_LAUNCHED(ctx);
+        ATE_CUDA(ctx, cudaMemcpyAsync(hflags, dflags, sizeof(int) * 3 * nfits, cudaMemcpyDeviceToHost, ctx->stream));
+        if (timing) { const double t = tnow(); t_host += t - t_mark; t_mark = t; }
+        ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (timing) { const double t = tnow(); t_wait += t - t_mark; t_mark = t; }
+        for (int id = 0; id < nfits; ++id) {
+            if (!rfits[id].live) continue;
+            hdone[id] = hflags[3 * (size_t)id];
+            hng[id] = hflags[3 * (size_t)id + 1];
+            hlmu[id] = hflags[3 * (size_t)id + 2];
+            ++age[id];
+        }
+        if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
     }
     if (timing)
         fprintf(stderr, "[ate timing] cv_binomial: %d rounds, host %.1f ms (planning + launches), waiting on the GPU %.1f ms\n",
