@@ -978,10 +978,12 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, 
         *packed_count = 0;
         return 0;
     }
-    // ---- row chunks: every CTA kind of a problem cuts the problem's rows the same way (so that the CTAs of
-    //      a chunk, scheduled together, walk the same rows and the L2 serves the repeats).  About three
-    //      waves of CTAs are laid out, the work of a problem deciding its share: the hardware scheduler
-    //      then evens out CTA kinds of different cost, and no SM idles because 148 does not divide evenly.
+    // ---- row chunks: every CTA kind of a problem cuts the problem's rows the same way (a fit's partials are
+    //      indexed by chunk).  About twelve waves of CTAs are laid out, the work of a problem deciding its
+    //      share, and handed out heaviest kind first: CTA kinds differ in cost by up to 2x (fits per CTA,
+    //      tiles per fit), so with few waves the tail of the launch idles most SMs (measured at C1:
+    //      3 waves 1690 ms per fit, 6 waves 1514, 12 waves 1483, heaviest first 1465; a CTA still runs
+    //      for hundreds of slots, its prologue is noise).
     std::vector<double> pcost(P, 0.0);
     std::vector<int> pkinds(P, 0), pchunks(P, 1);
     double total_cost = 0.0;
@@ -994,7 +996,7 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, 
         total_cost += g.cost;
     }
     {
-        static const int waves = getenv("ATE_ROUND_WAVES") ? std::max(1, atoi(getenv("ATE_ROUND_WAVES"))) : 3;
+        static const int waves = getenv("ATE_ROUND_WAVES") ? std::max(1, atoi(getenv("ATE_ROUND_WAVES"))) : 12;
         const double budget = (double)waves * ctx->num_sms;
         for (int p = 0; p < P; ++p) {
             if (!pkinds[p]) continue;
@@ -1082,6 +1084,7 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, 
     }
     RoundStats st;
     int ci = 0;
+    std::vector<double> cta_cost;
     for (int p = 0; p < P; ++p) {
         if (!pkinds[p]) continue;
         const long long nrows = probs[p].nrows;
@@ -1103,7 +1106,21 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, 
                 for (int wq = 0; wq < R_CWARPS; ++wq)
                     d.mma[wq] = make_uint2(half_word(g.warp_half[wq][0]), half_word(g.warp_half[wq][1]));
                 st.rows_staged += d.row_end - d.row_begin;
+                cta_cost.push_back(g.cost / std::max(1, g.chunks));
             }
+    }
+    {
+        // The hardware hands out CTAs in index order.  Heaviest kinds first (longest-processing-time order):
+        // the light CTAs then fill the tail of the launch.  ATE_ROUND_ORDER=0 keeps the chunk-major order
+        // (the kinds of a chunk side by side, walking the same rows at the same time).
+        static const int order = getenv("ATE_ROUND_ORDER") ? atoi(getenv("ATE_ROUND_ORDER")) : 1;
+        if (order == 1) {
+            std::vector<int> perm(nctas);
+            for (int i = 0; i < nctas; ++i) perm[i] = i;
+            std::stable_sort(perm.begin(), perm.end(), [&](int x, int y) { return cta_cost[x] > cta_cost[y]; });
+            std::vector<DCta> tmp(hc, hc + nctas);
+            for (int i = 0; i < nctas; ++i) hc[i] = tmp[perm[i]];
+        }
     }
     for (Group &g : groups) {
         const long long nrows = probs[g.prob].nrows;
