@@ -251,7 +251,9 @@ gather_rows_kernel(const double *__restrict__ X, long long ld, const int32_t *__
         const long long r = list ? (long long)__ldg(list + t) : t;
         const double2 *src = reinterpret_cast<const double2 *>(X + (size_t)r * (size_t)ld);
         double2 *dst = reinterpret_cast<double2 *>(Xp + (size_t)t * (size_t)ldp);
-        for (int c = lane; c < (int)(ldp / 2); c += 32) dst[c] = (2 * c < ncs) ? __ldg(src + c) : make_double2(0.0, 0.0);
+        // beyond the staged columns: the lists' zero column (ncs) and ONE column (ncs + 1), then zeros
+        for (int c = lane; c < (int)(ldp / 2); c += 32)
+            dst[c] = (2 * c < ncs) ? __ldg(src + c) : make_double2(0.0, 2 * c == ncs ? 1.0 : 0.0);
     }
 }
 

@@ -55,6 +55,7 @@ struct DProb {
     long long ld;
     const int32_t *rows;
     long long nrows;
+    int padded, pad_;
 };
 struct DFit {
     const double *coef;
@@ -63,7 +64,7 @@ struct DFit {
     double w;
     double *gram_part;  // [chunks][nblk][1024]
     double *eval_part;  // [chunks][3 ni + 3 R_EWARPS]
-    int nblk, pad;
+    int nblk, ones;     // ones >= 0: X^T v comes out of the Gram (RoundFit::ones)
 };
 struct DCta {
     int prob, nfit, chunk, pad;
@@ -74,7 +75,8 @@ struct DCta {
 struct DFold {
     const double *gram_part, *eval_part;
     double *sums, *H;
-    int nchunks, nblk, nG, ldh;
+    const int *colidx;
+    int nchunks, nblk, nG, ldh, ones, ni;
 };
 struct RArgs {
     const DProb *probs;
@@ -148,6 +150,8 @@ __device__ long long g_rtrace[TR_SLOTS * TR_EVENTS + 8];
 #ifndef ATE_MMA_UNROLL
 #define ATE_MMA_UNROLL 2
 #endif
+// one-hot code of a half's tile counts (na >= nb)
+__host__ __device__ constexpr unsigned pat_bit(int na, int nb) { return 1u << (na * 5 + nb); }
 constexpr int MMA_UNROLL = ATE_MMA_UNROLL;  // k-steps per trip of the loop below (A/B builds: tools/build_variant_lib.sh)
 template <int NA, int NB, int ROWS>
 __device__ __forceinline__ void mma_half_slot(double (&accA)[4][2], double (&accB)[4][2], const char *sbase, uint32_t kstep_bytes,
@@ -155,16 +159,29 @@ __device__ __forceinline__ void mma_half_slot(double (&accA)[4][2], double (&acc
 #pragma unroll(MMA_UNROLL)
     for (int kk = 0; kk < ROWS / 4; ++kk) {
         const char *rowp = sbase + (size_t)kk * kstep_bytes;  // (warp-uniform)
+#ifdef ATE_MMA_NOLOAD  // measurement only: the DMMA stream of this loop without its operand loads
+        const double vv = 1.0 + kk;
+        double fb[NA];
+#pragma unroll
+        for (int n = 0; n < NA; ++n) fb[n] = __longlong_as_double((long long)offB[n] + kk);
+        const double fa = __longlong_as_double((long long)offA0 + kk) * vv;
+        (void)rowp; (void)vs;
+#else
         const double vv = vs[kk * 4];
         // v scales the A operand (one or two products per k-step) rather than the NA B operands
         double fb[NA];
 #pragma unroll
         for (int n = 0; n < NA; ++n) fb[n] = *reinterpret_cast<const double *>(rowp + offB[n]);
         const double fa = *reinterpret_cast<const double *>(rowp + offA0) * vv;
+#endif
 #pragma unroll
         for (int n = 0; n < NA; ++n) dmma884(accA[n][0], accA[n][1], fa, fb[n]);
         if (NB > 0) {
+#ifdef ATE_MMA_NOLOAD
+            const double fa1 = __longlong_as_double((long long)offA1 + kk) * vv;
+#else
             const double fa1 = *reinterpret_cast<const double *>(rowp + offA1) * vv;
+#endif
 #pragma unroll
             for (int n = 0; n < NB; ++n) dmma884(accB[n][0], accB[n][1], fa1, fb[n]);
         }
@@ -209,14 +226,14 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
     const long long c_begin = scta.row_begin, c_end = scta.row_end;
     const int nit = (int)((c_end - c_begin + ROWS - 1) / ROWS);
     const int nfit = scta.nfit;
-    const bool contiguous = (prob.rows == nullptr && prob.ld == (long long)pitch);
+    const bool contiguous = (prob.rows == nullptr && prob.ld == (long long)pitch && prob.padded != 0);
     // warp roles: 0-7 MMA, 8 producer, 9 second producer (row-list mode) or third helper, 10-11 helpers, 12-15 eval
     const int nhelp = contiguous ? 3 : 2;
     const bool is_producer = (warp == R_PRODUCER) || (warp == R_PRODUCER + 1 && !contiguous);
     const int hidx = (warp == R_HELPER) ? 0 : (warp == R_HELPER + 1) ? 1 : (warp == R_PRODUCER + 1 && contiguous) ? 2 : -1;
 
-    for (int e = threadIdx.x; e < stages * ROWS * R_PAD; e += blockDim.x)
-        sx[(size_t)(e / R_PAD) * pitch + ncols + (e % R_PAD)] = 0.0;  // the list's "zero column"
+    for (int e = threadIdx.x; e < stages * ROWS * R_PAD; e += blockDim.x)  // the lists' "zero column" and "one column"
+        sx[(size_t)(e / R_PAD) * pitch + ncols + (e % R_PAD)] = (e % R_PAD) == 1 ? 1.0 : 0.0;
     if (threadIdx.x == 0) {
         for (int s = 0; s < stages; ++s) {
             mbar_init(full + s, contiguous ? 1 : R_PWARPS);
@@ -541,6 +558,7 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             // FMA pipe is cheaper here and leaves the DMMA pipe to the Gram.  Lanes own column pairs, the
             // columns are split between the helper warps.
             const int npairs = ncols >> 1, ppw = (npairs + nhelp - 1) / nhelp;
+            const bool xtv_from_gram = nfit > 0 && a.fits[scta.fit[0]].ones >= 0;
             double gr[2 * ITERH], hx[2 * ITERH], hxx[INIT ? 2 * ITERH : 1];
 #pragma unroll
             for (int i = 0; i < 2 * ITERH; ++i) {
@@ -559,27 +577,46 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
                 wait_g(full + s, ph, whint);
                 if (any_lead && !(a.skip & 2)) {
                     wait_g(vfull + s, ph, whint);
+                    if (h < 2) RTRACE(5 + h, it);  // helper h: start
                     const double *slot = sx + stage_doubles * s;
-#pragma unroll 2
-                    for (int r = 0; r < ROWS; ++r) {
-                        const double *rowp = slot + (size_t)r * pitch;
-                        const double vj = sv[(size_t)s * FMAX * ROWS + r];
-                        const double rj = sr[(size_t)s * FMAX * ROWS + r];
+                    if (!INIT && xtv_from_gram) {
+                        // X^T v of the list columns comes out of the Gram (its ONE column): X^T r alone here.
+                        // Under the MMA warps' DMMA stream every fp64 FMA of a helper waits its turn on the
+                        // shared pipe, and the helpers of a single-fit CTA paced the whole ring (measured).
+#pragma unroll 4
+                        for (int r = 0; r < ROWS; ++r) {
+                            const double *rowp = slot + (size_t)r * pitch;
+                            const double rj = sr[(size_t)s * FMAX * ROWS + r];
 #pragma unroll
-                        for (int i = 0; i < ITERH; ++i) {
-                            const double2 x = col[i] >= 0 ? *reinterpret_cast<const double2 *>(rowp + col[i]) : make_double2(0.0, 0.0);
-                            gr[2 * i] = fma(rj, x.x, gr[2 * i]);
-                            gr[2 * i + 1] = fma(rj, x.y, gr[2 * i + 1]);
-                            hx[2 * i] = fma(vj, x.x, hx[2 * i]);
-                            hx[2 * i + 1] = fma(vj, x.y, hx[2 * i + 1]);
-                            if (INIT) {
-                                hxx[2 * i] = fma(vj * x.x, x.x, hxx[2 * i]);
-                                hxx[2 * i + 1] = fma(vj * x.y, x.y, hxx[2 * i + 1]);
+                            for (int i = 0; i < ITERH; ++i) {
+                                const double2 x = col[i] >= 0 ? *reinterpret_cast<const double2 *>(rowp + col[i]) : make_double2(0.0, 0.0);
+                                gr[2 * i] = fma(rj, x.x, gr[2 * i]);
+                                gr[2 * i + 1] = fma(rj, x.y, gr[2 * i + 1]);
+                            }
+                        }
+                    } else {
+#pragma unroll 2
+                        for (int r = 0; r < ROWS; ++r) {
+                            const double *rowp = slot + (size_t)r * pitch;
+                            const double vj = sv[(size_t)s * FMAX * ROWS + r];
+                            const double rj = sr[(size_t)s * FMAX * ROWS + r];
+#pragma unroll
+                            for (int i = 0; i < ITERH; ++i) {
+                                const double2 x = col[i] >= 0 ? *reinterpret_cast<const double2 *>(rowp + col[i]) : make_double2(0.0, 0.0);
+                                gr[2 * i] = fma(rj, x.x, gr[2 * i]);
+                                gr[2 * i + 1] = fma(rj, x.y, gr[2 * i + 1]);
+                                hx[2 * i] = fma(vj, x.x, hx[2 * i]);
+                                hx[2 * i + 1] = fma(vj, x.y, hx[2 * i + 1]);
+                                if (INIT) {
+                                    hxx[2 * i] = fma(vj * x.x, x.x, hxx[2 * i]);
+                                    hxx[2 * i + 1] = fma(vj * x.y, x.y, hxx[2 * i + 1]);
+                                }
                             }
                         }
                     }
                 }
                 __syncwarp();
+                if (h < 2) RTRACE(7 + h, it);  // helper h: done
                 if (lane == 0) mbar_arrive(empty + s);
             }
             if (nfit > 0 && scta.lead[0] != 0) {
@@ -624,7 +661,8 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
             for (int n = 0; n < 4; ++n)
                 offB[hh][n] = (uint32_t)((cnt > 0 ? __ldg(colidx + (4 * seg[hh] + n) * 8 + g) : 0) + k4 * pitch) * 8u;
             any |= cnt > 0;
-            pat[hh] = nt[2 * hh] * 5 + nt[2 * hh + 1];  // the planner puts the heavier tile row first
+            // the planner puts the heavier tile row first; (0, 0) is an empty half
+            pat[hh] = nt[2 * hh] > 0 ? (int)pat_bit(nt[2 * hh], nt[2 * hh + 1]) : 0;
         }
         const uint32_t kstep_bytes = (uint32_t)pitch * 32u;  // four rows per k-step
         double acc[4][4][2];
@@ -640,24 +678,24 @@ __global__ void __launch_bounds__(R_THREADS, 1) irls_round_kernel(const RArgs a)
                 wait_g(vfull + s, ph, whint);
                 if (warp < 3) RTRACE(9 + 2 * warp, it);  // MMA warp 0..2: start
                 const char *sbase = reinterpret_cast<const char *>(sx + stage_doubles * s);
+#ifdef ATE_MMA_TWICE  // measurement only: every slot's DMMA work issued twice
+                for (int rep = 0; rep < 2; ++rep)
+#endif
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
                     const double *vs = sv + ((size_t)s * FMAX + fsl[hh]) * ROWS + k4;
-                    // one (warp-uniform) dispatch per half and slot, then straight-line loops
+                    // one (warp-uniform) dispatch per half and slot, then straight-line loops.  The pattern is
+                    // a ONE-HOT mask tested bit by bit, commonest first: a switch over dense codes becomes a
+                    // jump table (LDC + BRX + WARPSYNC, ~90 cycles per dispatch, measured), a bit test is a
+                    // predicated branch.
 #define MMA_HALF(NA_, NB_)                                                                                          \
-    case (NA_) * 5 + (NB_):                                                                                          \
+    if (pat[hh] & pat_bit(NA_, NB_)) {                                                                               \
         mma_half_slot<NA_, NB_, ROWS>(acc[2 * hh], acc[2 * hh + 1], sbase, kstep_bytes, vs, offA[2 * hh], offA[2 * hh + 1], \
                                       offB[hh]);                                                                     \
-        break;
-                    switch (pat[hh]) {
-                        MMA_HALF(4, 4) MMA_HALF(4, 3) MMA_HALF(4, 2) MMA_HALF(4, 1) MMA_HALF(4, 0)
-                        MMA_HALF(3, 2) MMA_HALF(3, 1) MMA_HALF(3, 0)
-                        MMA_HALF(2, 1) MMA_HALF(2, 0)
-                        MMA_HALF(1, 0)
-                        default:
-                            if (pat[hh] != 0) __trap();  // not a pair the planner deals (an empty half is 0)
-                            break;
-                    }
+    } else
+                    MMA_HALF(4, 4) MMA_HALF(4, 3) MMA_HALF(4, 2) MMA_HALF(4, 1) MMA_HALF(3, 2) MMA_HALF(4, 0)
+                    MMA_HALF(3, 1) MMA_HALF(2, 1) MMA_HALF(3, 0) MMA_HALF(2, 0) MMA_HALF(1, 0)
+                    if (pat[hh] != 0) __trap();  // not a pair the planner deals (an empty half is 0)
 #undef MMA_HALF
                 }
             }
@@ -693,6 +731,10 @@ round_fold_eval_kernel(const DFold *__restrict__ folds, int ni, int init) {
     if (e >= plen) return;
     double s = 0.0;
     if (e < 3 * ni) {
+        if (fd.ones >= 0 && e >= ni && e < 2 * ni) {  // X^T v: the list columns' entries are written by
+            if (lane == 0) fd.sums[e] = 0.0;          // round_fold_gram_kernel (launched after this one) from
+            return;                                   // the Gram's ONE column; the solve reads no others
+        }
         if (e < 2 * ni || init)
             for (int q = lane; q < fd.nchunks; q += 32) s += fd.eval_part[(size_t)q * ep + e];
     } else {
@@ -722,6 +764,8 @@ round_fold_gram_kernel(const DFold *__restrict__ folds) {
         for (int q = 0; q < fd.nchunks; ++q) s += src[q * stride];
     }
     fd.H[e] = s;
+    // the ONE column of the list: H[c][ones] = sum_i v_i x_i,c = (X^T v)[colidx[c]]
+    if (fd.ones >= 0 && c == fd.ones && r < fd.ones) fd.sums[fd.ni + fd.colidx[r]] = s;
 }
 
 // ---- host: who computes which Gram tiles ----------------------------------------------------------
@@ -788,6 +832,39 @@ void deal_halves(Group &g) {
         if (best < 0) return;  // cannot happen: the caller admits at most 2 R_CWARPS halves
         g.warp_half[best][cnt[best]++] = h;
         load[best] += h.load;
+    }
+    // The slot is released when the SLOWEST warp is through its tiles (an MMA warp issues its DMMAs at its
+    // own pace, whatever the other warp of its sub-partition does), so the busiest warp paces the ring:
+    // while it helps, move one tile row out of a two-row half of the busiest warp to the lightest warp that
+    // still has a free half (both then hold single-row halves of that segment).
+    auto row_tiles = [](const Half &h, int j) { const int t = h.rows[j] - 4 * h.seg + 1; return t < 4 ? t : 4; };
+    for (int pass = 0; pass < 4 * R_CWARPS; ++pass) {
+        int hi = 0, lo = -1;
+        for (int w = 1; w < R_CWARPS; ++w)
+            if (load[w] > load[hi]) hi = w;
+        for (int w = 0; w < R_CWARPS; ++w)
+            if (w != hi && cnt[w] < 2 && (lo < 0 || load[w] < load[lo])) lo = w;
+        if (lo < 0) break;
+        int bq = -1, bj = -1, bt = 0;  // the row whose move lowers max(load[hi], load[lo]) most
+        for (int q = 0; q < cnt[hi]; ++q) {
+            const Half &h = g.warp_half[hi][q];
+            if (h.cnt != 2) continue;
+            for (int j = 0; j < 2; ++j) {
+                const int t = row_tiles(h, j);
+                const int worst = std::max(load[hi] - t, load[lo] + t);
+                if (worst < load[hi] && (bq < 0 || worst < std::max(load[hi] - bt, load[lo] + bt))) {
+                    bq = q; bj = j; bt = t;
+                }
+            }
+        }
+        if (bq < 0) break;
+        Half &h = g.warp_half[hi][bq];
+        Half moved{h.fit, h.seg, 1, bt, {h.rows[bj], 0}};
+        const int keep = h.rows[1 - bj];
+        h.rows[0] = keep; h.rows[1] = 0; h.cnt = 1; h.load -= bt;
+        g.warp_half[lo][cnt[lo]++] = moved;
+        load[hi] -= bt;
+        load[lo] += bt;
     }
 }
 
@@ -1059,7 +1136,7 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, 
     DFit *hf = (DFit *)((char *)hst + o_fits);
     DCta *hc = (DCta *)((char *)hst + o_ctas);
     DFold *hd = (DFold *)((char *)hst + o_folds);
-    for (int p = 0; p < P; ++p) hp[p] = DProb{probs[p].X, probs[p].ld, probs[p].rows, probs[p].nrows};
+    for (int p = 0; p < P; ++p) hp[p] = DProb{probs[p].X, probs[p].ld, probs[p].rows, probs[p].nrows, probs[p].padded, 0};
     int li = 0;
     for (int f = 0; f < nfits; ++f) {
         if (!fits[f].live) continue;
@@ -1080,6 +1157,10 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, 
         hd[li].nblk = nblk;
         hd[li].nG = fits[f].nG;
         hd[li].ldh = slots[f].ldh;
+        hd[li].colidx = fits[f].colidx;
+        hd[li].ones = init ? -1 : fits[f].ones;
+        hd[li].ni = ni;
+        hf[f].ones = init ? -1 : fits[f].ones;
         ++li;
     }
     RoundStats st;
@@ -1230,7 +1311,7 @@ extern "C" int ate_round_kernel_bench(ate_ctx *ctx, long long nrows, int ni, int
             for (long long r = 0; r < cnt; ++r)
                 for (long long c = 0; c < ld; ++c) {
                     const unsigned h = (unsigned)((r0 + r) * 2654435761u + c * 40503u);
-                    row[r * ld + c] = c < ni ? ((h >> 8) & 1023) / 512.0 - 1.0 : (c == iy ? (double)((h >> 5) & 1) : (c == ni + 2 && !private_copy ? 1.0 : 0.0));
+                    row[r * ld + c] = c < ni ? ((h >> 8) & 1023) / 512.0 - 1.0 : (c == iy ? (double)((h >> 5) & 1) : ((c == ni + 2 && !private_copy) || (c == ncs + 1 && private_copy) ? 1.0 : 0.0));
                 }
             ATE_CUDA(ctx, cudaMemcpyAsync(dX + (size_t)r0 * ld, row.data(), sizeof(double) * (size_t)cnt * ld, cudaMemcpyHostToDevice, ctx->stream));
             ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1243,6 +1324,7 @@ extern "C" int ate_round_kernel_bench(ate_ctx *ctx, long long nrows, int ni, int
                 hc[(size_t)f * (ni + 1) + hl[(size_t)f * ldh + j]] = 0.01 * ((j % 5) - 2);
             }
             hc[(size_t)f * (ni + 1) + ni] = -0.3;
+            if (list_cols >= R_ONES_MIN) hl[(size_t)f * ldh + list_cols - 1] = ncs + 1;  // as the driver does: the ONE column closes a wide list
         }
         ATE_CUDA(ctx, cudaMemcpyAsync(dcoef, hc.data(), cb, cudaMemcpyHostToDevice, ctx->stream));
         ATE_CUDA(ctx, cudaMemcpyAsync(dlist, hl.data(), lb, cudaMemcpyHostToDevice, ctx->stream));
@@ -1250,7 +1332,7 @@ extern "C" int ate_round_kernel_bench(ate_ctx *ctx, long long nrows, int ni, int
     }
     std::vector<RoundProblem> probs(nprob);
     std::vector<RoundFit> fits(nfits);
-    for (int p = 0; p < nprob; ++p) probs[p] = RoundProblem{dX + (size_t)p * nrows * ld, ld, nullptr, nrows};
+    for (int p = 0; p < nprob; ++p) probs[p] = RoundProblem{dX + (size_t)p * nrows * ld, ld, nullptr, nrows, private_copy ? 1 : 0};
     for (int f = 0; f < nfits; ++f) {
         RoundFit &r = fits[f];
         r.prob = f / fits_per_prob;
@@ -1261,6 +1343,7 @@ extern "C" int ate_round_kernel_bench(ate_ctx *ctx, long long nrows, int ni, int
         r.coef = dcoef + (size_t)f * (ni + 1);
         r.colidx = dlist + (size_t)f * ldh;
         r.nG = list_cols;
+        r.ones = list_cols >= R_ONES_MIN ? list_cols - 1 : -1;
         r.live = 1;
     }
     std::vector<RoundSlot> slots;

@@ -8,12 +8,17 @@
 
 #include "common.cuh"
 
+// Lists of at least this many columns end with the staged rows' ONE column (RoundFit::ones): such a list
+// is served by a CTA of its own, whose helpers then compute X^T r only.
+constexpr int R_ONES_MIN = 65;
+
 // one cv.glmnet problem = one set of rows, as this rank holds it
 struct RoundProblem {
     const double *X;      // private contiguous copy of the rows (rows == NULL, ld == ncs + 4: a slot
     long long ld;         //   is ONE bulk copy) or the shared design read through a row list
     const int32_t *rows;  // device row ids or NULL
     long long nrows;      // rows held by this rank
+    int padded;           // 1: a private copy whose rows end with the pad [0, 1, 0, 0] (zero and ONE column)
 };
 
 // one path fit, this round
@@ -25,6 +30,9 @@ struct RoundFit {
     const double *coef;                // device: ni raw-scale coefficients, then the intercept
     const int *colidx;                 // device: the Gram's column list, padded to a multiple of 32 with ncs
     int nG;                            // columns in the list (0: evaluation only)
+    int ones;                          // >= 0: list position ones holds the staged rows' ONE column (index
+                                       // ncs + 1); X^T v of the list columns is then row `ones` of the Gram and
+                                       // the helpers skip it.  -1: the helpers compute X^T v
     int live;                          // 0: skip this fit
 };
 

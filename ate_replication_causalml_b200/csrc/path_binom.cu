@@ -37,7 +37,7 @@ namespace {
 
 enum { PH_INIT = 0, PH_REFRESH = 1 };
 enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_SUMS, SD_SUMS2, SD_SUMA, SD_N };
-enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_NG, SI_RETRY, SI_MISS, SI_N };
+enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_NG, SI_RETRY, SI_MISS, SI_ONES, SI_N };
 // sums layout: gr[ni] = X^T r, hx[ni] = X^T v, hxx[ni] = sum v x^2, then XMZ, SR, DEV
 enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
 
@@ -139,6 +139,7 @@ lognet_init_kernel(const LognetFit *__restrict__ fits, const double *__restrict_
         sd[SD_BZ] = bz;
         sd[SD_B0] = bz;
         si[SI_PHASE] = PH_INIT;
+        si[SI_ONES] = -1;
         if (q0 <= GLM_PMIN) {
             si[SI_JERR] = 8001;
             si[SI_DONE] = 1;
@@ -402,7 +403,8 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
 // H holds X_L^T V X_L over the column list L the step used (positions gpos).  At the end the list for
 // the next step is rebuilt: the strong set plus every column whose gradient is within 10 % of the
 // next strong-rule / KKT threshold, ordered so that the MMA warps' gathered operand loads spread over
-// the shared-memory banks.  flags_out[3 fit + {0, 1, 2}] = {done, length of the next list, lambdas recorded}.
+// the shared-memory banks.  flags_out[4 fit + {0, 1, 2, 3}] = {done, length of the next list, lambdas recorded, position of the
+// ONE column in that list or -1}.
 __global__ void __launch_bounds__(CD_THREADS)
 lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev, int *__restrict__ flags_out) {
     const LognetFit f = fits[blockIdx.x];
@@ -412,9 +414,10 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
     double *sd = fit_scal_d(f);
     if (si[SI_DONE] || !si[SI_SOLVE] || !rd.live) {
         if (tid == 0) {
-            flags_out[3 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
-            flags_out[3 * blockIdx.x + 1] = si[SI_DONE] ? 0 : si[SI_NG];
-            flags_out[3 * blockIdx.x + 2] = si[SI_LMU];
+            flags_out[4 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
+            flags_out[4 * blockIdx.x + 1] = si[SI_DONE] ? 0 : si[SI_NG];
+            flags_out[4 * blockIdx.x + 2] = si[SI_LMU];
+            flags_out[4 * blockIdx.x + 3] = si[SI_ONES];
         }
         return;
     }
@@ -622,10 +625,20 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
         for (int q = 0; q < 4; ++q)
             while (cnt4[q]-- > 0) glist[out++] = srt[pos4[q]++];
         for (int c = 0; c < nG; ++c) Ggpos[glist[c]] = c;
+        // A wide list gets a CTA of its own in the step kernel, whose helpers are its slowest warps: such a
+        // list ends with the staged rows' ONE column, the Gram's row of that column IS X^T v of the list
+        // columns (all the solve reads of it), and the helpers compute X^T r only.
+        int ones = -1;
+        if (nG + 1 >= R_ONES_MIN && nG < f.ldh) {
+            ones = nG;
+            glist[nG++] = f.ncs + 1;
+        }
         const int npad = (nG + 31) / 32 * 32;
         for (int c = nG; c < npad && c < f.ldh; ++c) glist[c] = f.ncs;
         si[SI_NG] = nG;
-        flags_out[3 * blockIdx.x + 1] = nG;
+        si[SI_ONES] = ones;
+        flags_out[4 * blockIdx.x + 1] = nG;
+        flags_out[4 * blockIdx.x + 3] = ones;
         if (!retry) {
             f.coef[ni] = b0 - dotbm;
             sd[SD_B0] = b0;
@@ -637,8 +650,8 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
                 si[SI_DONE] = 1;
             }
         }
-        flags_out[3 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
-        flags_out[3 * blockIdx.x + 2] = si[SI_LMU];
+        flags_out[4 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
+        flags_out[4 * blockIdx.x + 2] = si[SI_LMU];
     }
 }
 
@@ -677,6 +690,9 @@ lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, int LC,
             x[2 * i + 1] = c + 1 < ni ? t2.y : 0.0;
         }
         const double yi = __ldg(xr + f.iy);
+        // lane l keeps eta of lambdas l and l + 32 of the chunk; the deviance terms are then evaluated by
+        // all lanes at once (one exp / log sequence per 32 lambdas instead of one per lambda)
+        double eta0 = 0.0, eta1 = 0.0;
         for (int m = 0; m < mc; ++m) {
             const double *bm = sb + (size_t)m * ni;
             double dot = 0.0;
@@ -688,13 +704,24 @@ lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, int LC,
             }
             const double eta = sa0[m] + warp_sum(dot);
             if ((m & 31) == lane) {
-                double pr = 1.0 / (1.0 + exp(-eta));
-                pr = fmin(fmax(pr, 1.0e-5), 1.0 - 1.0e-5);
-                const double dv = -2.0 * (yi * log(pr) + (1.0 - yi) * log(1.0 - pr));
                 if (m < 32)
-                    acc0 += dv;
+                    eta0 = eta;
                 else
+                    eta1 = eta;
+            }
+        }
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+            if (hh * 32 >= mc) break;  // (warp-uniform)
+            const double eta = hh ? eta1 : eta0;
+            double pr = 1.0 / (1.0 + exp(-eta));
+            pr = fmin(fmax(pr, 1.0e-5), 1.0 - 1.0e-5);
+            const double dv = -2.0 * (yi * log(pr) + (1.0 - yi) * log(1.0 - pr));
+            if (lane + 32 * hh < mc) {
+                if (hh)
                     acc1 += dv;
+                else
+                    acc0 += dv;
             }
         }
     }
@@ -838,7 +865,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         dpart = cv.take<double>((size_t)ev_blocks * nlam);
         dcv = cv.take<double>((size_t)(nfol > 0 ? nfol : 1) * nlam);
         dsti = cv.take<int>(si_len * nfits);
-        dflags = cv.take<int>(3 * (size_t)nfits);
+        dflags = cv.take<int>(4 * (size_t)nfits);
         dnl = cv.take<int>(1);
         dfits = cv.take<LognetFit>(nfits);
         drdev = cv.take<RoundDev>(nfits);
@@ -850,7 +877,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         }
     }
     ATE_CUDA(ctx, cudaMemsetAsync(dout, 0, sizeof(double) * out_len * nfits, ctx->stream));
-    ATE_CUDA(ctx, cudaMemsetAsync(dflags, 0, sizeof(int) * 3 * nfits, ctx->stream));
+    ATE_CUDA(ctx, cudaMemsetAsync(dflags, 0, sizeof(int) * 4 * nfits, ctx->stream));
     if (vp_host) ATE_CUDA(ctx, cudaMemcpyAsync(dvp, vp_host, sizeof(double) * ni, cudaMemcpyHostToDevice, ctx->stream));
     if (po.flmin >= 1.0) {
         ATE_CUDA(ctx, cudaMemcpyAsync(dulam, po.ulam, sizeof(double) * nlam, cudaMemcpyHostToDevice, ctx->stream));
@@ -886,6 +913,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         rprobs[p].ld = Xp[p] ? ldp : ld;
         rprobs[p].rows = Xp[p] ? nullptr : probs[p].d_list;
         rprobs[p].nrows = probs[p].nt;
+        rprobs[p].padded = Xp[p] ? 1 : 0;
     }
     // fit ids: [0, nlead) the full-data fits, then problem-major the cv-fold fits
     std::vector<LognetFit> hf(nfits);
@@ -958,9 +986,9 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     auto tnow = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     double t_host = 0.0, t_wait = 0.0, t_mark = tnow();
 
-    std::vector<int> hdone(nfits, 0), hng(nfits, 0), hlmu(nfits, 0), age(nfits, -1);
+    std::vector<int> hdone(nfits, 0), hng(nfits, 0), hlmu(nfits, 0), hones(nfits, -1), age(nfits, -1);
     void *hflags_v = nullptr, *hrdev_v = nullptr;
-    ATE_TRY(ate_cached_pinned(ctx, "binom.hflags", sizeof(int) * 3 * (size_t)nfits, &hflags_v));
+    ATE_TRY(ate_cached_pinned(ctx, "binom.hflags", sizeof(int) * 4 * (size_t)nfits, &hflags_v));
     ATE_TRY(ate_cached_pinned(ctx, "binom.hrdev", sizeof(RoundDev) * (size_t)nfits, &hrdev_v));
     int *hflags = (int *)hflags_v;
     RoundDev *hrdev = (RoundDev *)hrdev_v;
@@ -1001,6 +1029,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             r.coef = hf[id].coef;
             r.colidx = hf[id].st_i + 6 * (size_t)ni + ldh;  // the list the last solve left
             r.nG = hng[id];
+            r.ones = hones[id];
         }
         if (!live) break;
         // the first step of a fit also needs sum v x^2 of every column: a launch of its own (other template
@@ -1039,15 +1068,16 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         }
         lognet_solve_kernel<<<nfits, CD_THREADS, cd_smem, ctx->stream>>>(dfits, drdev, dflags);
         ATE_LAUNCHED(ctx);
-        ATE_CUDA(ctx, cudaMemcpyAsync(hflags, dflags, sizeof(int) * 3 * nfits, cudaMemcpyDeviceToHost, ctx->stream));
+        ATE_CUDA(ctx, cudaMemcpyAsync(hflags, dflags, sizeof(int) * 4 * nfits, cudaMemcpyDeviceToHost, ctx->stream));
         if (timing) { const double t = tnow(); t_host += t - t_mark; t_mark = t; }
         ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         if (timing) { const double t = tnow(); t_wait += t - t_mark; t_mark = t; }
         for (int id = 0; id < nfits; ++id) {
             if (!rfits[id].live) continue;
-            hdone[id] = hflags[3 * (size_t)id];
-            hng[id] = hflags[3 * (size_t)id + 1];
-            hlmu[id] = hflags[3 * (size_t)id + 2];
+            hdone[id] = hflags[4 * (size_t)id];
+            hng[id] = hflags[4 * (size_t)id + 1];
+            hlmu[id] = hflags[4 * (size_t)id + 2];
+            hones[id] = hflags[4 * (size_t)id + 3];
             ++age[id];
         }
         if (++rounds > max_rounds) return ate_fail(ctx, -2, "cv_binomial: IRLS round cap hit");
