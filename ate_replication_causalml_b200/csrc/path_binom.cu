@@ -604,10 +604,10 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
         for (int c = 0; c < nS; ++c) cand[nG++] = sl[c];
         for (int k = 0; k < ni && nG < f.ldh; ++k)
             if (!ixx[k] && Gju[k] && fabs(g[k]) > tnext * vq[k]) cand[nG++] = k;
-        // Order of the list.  An MMA warp loads, per 8x8 tile, 8 list columns x 4 staged rows; the rows
-        // sit 4 (mod 8) doubles apart, so the 8 columns spread evenly over the 16 eight-byte banks exactly
-        // when every residue class mod 4 holds two of them.  Deal the columns into groups of eight that
-        // way while all four classes last; the remainder follows in any order.
+        // Order of the list.  An MMA warp loads, per 8x8 tile, 8 list columns x 4 staged rows; consecutive
+        // rows sit 12 (mod 16) doubles apart, so four columns x four rows hit the 16 eight-byte banks once
+        // each exactly when the four columns have four different residues mod 4.  Deal the columns into
+        // such groups of four while all four classes last.
         int cnt4[4] = {0, 0, 0, 0}, beg4[4], pos4[4];
         for (int c = 0; c < nG; ++c) cnt4[cand[c] & 3]++;
         beg4[0] = 0;
@@ -616,14 +616,23 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
         for (int c = 0; c < nG; ++c) srt[pos4[cand[c] & 3]++] = cand[c];
         for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
         int out = 0;
-        while (cnt4[0] >= 2 && cnt4[1] >= 2 && cnt4[2] >= 2 && cnt4[3] >= 2)
+        // (a 64-bit shared load is served half a warp at a time, i.e. FOUR consecutive list columns x four
+        // rows: every aligned group of four must hold all four classes -- class order 0 1 2 3 0 1 2 3, not
+        // 0 0 1 1 2 2 3 3, which cost 40 % extra wavefronts in the C1 capture)
+        while (cnt4[0] >= 1 && cnt4[1] >= 1 && cnt4[2] >= 1 && cnt4[3] >= 1)
             for (int q = 0; q < 4; ++q) {
                 glist[out++] = srt[pos4[q]++];
-                glist[out++] = srt[pos4[q]++];
-                cnt4[q] -= 2;
+                cnt4[q] -= 1;
             }
-        for (int q = 0; q < 4; ++q)
-            while (cnt4[q]-- > 0) glist[out++] = srt[pos4[q]++];
+        for (bool any = true; any;) {  // the remainder: the classes that are left, still taking turns
+            any = false;
+            for (int q = 0; q < 4; ++q)
+                if (cnt4[q] > 0) {
+                    glist[out++] = srt[pos4[q]++];
+                    --cnt4[q];
+                    any = true;
+                }
+        }
         for (int c = 0; c < nG; ++c) Ggpos[glist[c]] = c;
         // A wide list gets a CTA of its own in the step kernel, whose helpers are its slowest warps: such a
         // list ends with the staged rows' ONE column, the Gram's row of that column IS X^T v of the list
