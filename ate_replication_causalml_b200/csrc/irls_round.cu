@@ -813,11 +813,16 @@ struct Group {
 
 // two halves per warp: heaviest first onto the lightest warp that has room, preferring a warp that
 // already holds a half of the same fit and segment (its B operands are then loaded once)
-void deal_halves(Group &g) {
+// `handicap`: tiles per k-step an MMA warp of sub-partitions 1-3 starts with.  MMA warp w runs on
+// sub-partition w % 4; the three helper warps sit on sub-partitions 1-3 and their X^T r / X^T v tiles use
+// the same fp64 datapath (staged columns / 8 tiles per k-step in a CTA of several fits), while
+// sub-partition 0 holds only the producer -- its two MMA warps take more of the Gram.
+void deal_halves(Group &g, int handicap) {
     for (int w = 0; w < R_CWARPS; ++w) g.warp_half[w][0] = g.warp_half[w][1] = Half{0, 0, 0, 0, {0, 0}};
     std::vector<Half> hs = g.halves;
     std::stable_sort(hs.begin(), hs.end(), [](const Half &x, const Half &y) { return x.load > y.load; });
     int cnt[R_CWARPS] = {0}, load[R_CWARPS] = {0};
+    for (int w = 0; w < R_CWARPS; ++w) load[w] = (w & 3) ? handicap : 0;
     for (const Half &h : hs) {
         int best = -1;
         for (int w = 0; w < R_CWARPS; ++w) {
@@ -873,7 +878,12 @@ void deal_halves(Group &g) {
 // sums); the others are packed first-fit, up to `fmax` fits and 2 R_CWARPS halves per CTA.
 // Returns -1 for a list the tile numbering cannot hold.
 int build_groups(int P, const std::vector<int> &prob_of, const std::vector<int> &live, const std::vector<int> &nGs,
-                 int fmax, std::vector<Group> &groups) {
+                 int fmax, int ncs, std::vector<Group> &groups) {
+    // helper tiles per k-step and MMA warp of sub-partitions 1-3 (two MMA warps each): DMMA helpers of a
+    // CTA with several fits issue ncs / 8 tiles over three warps; the FMA helpers of a single fit cost
+    // about a tile's worth of pipe time per warp
+    static const int hc_scale = getenv("ATE_ROUND_HANDICAP") ? atoi(getenv("ATE_ROUND_HANDICAP")) : 100;  // percent (A/B measurements)
+    const int hc_multi = (ncs / 8 + 5) / 6 * hc_scale / 100, hc_single = 1 * hc_scale / 100;
     const int nfits = (int)prob_of.size();
     const int cap = 2 * R_CWARPS;
     std::vector<Half> hv;
@@ -906,7 +916,7 @@ int build_groups(int P, const std::vector<int> &prob_of, const std::vector<int> 
                 for (int q = 0; q < ng; ++q) {
                     Group &g = parts[q];
                     g.prob = p; g.nfit = 1; g.fit[0] = f; g.lead[0] = (q == 0);
-                    deal_halves(g);
+                    deal_halves(g, q == 0 ? hc_single : 0);
                     groups.push_back(g);
                 }
                 continue;
@@ -935,7 +945,7 @@ int build_groups(int P, const std::vector<int> &prob_of, const std::vector<int> 
             }
         }
         for (Group &g : open) {
-            deal_halves(g);
+            deal_halves(g, g.nfit > 1 && fmax > 1 ? hc_multi : hc_single);
             groups.push_back(g);
         }
     }
@@ -984,7 +994,7 @@ extern "C" int ate_round_plan_describe(int nfit, const int *list_cols, int stage
     const int fmax = round_fmax(staged_cols, 0);
     std::vector<int> prob_of(nfit, 0), live(nfit, 1), nGs(list_cols, list_cols + nfit);
     std::vector<Group> groups;
-    if (build_groups(1, prob_of, live, nGs, fmax, groups) < 0) return -1;
+    if (build_groups(1, prob_of, live, nGs, fmax, staged_cols, groups) < 0) return -1;
     if ((int)groups.size() > max_groups) return -2;
     for (size_t gi = 0; gi < groups.size(); ++gi) {
         unsigned *d = desc + 24 * gi;
@@ -1048,7 +1058,7 @@ int ate_i_irls_round(ate_ctx *ctx, int ncs, int ni, int iy, int init, int bank, 
             live[f] = fits[f].live;
             nGs[f] = fits[f].nG;
         }
-        if (build_groups(P, prob_of, live, nGs, fmax, groups) < 0)
+        if (build_groups(P, prob_of, live, nGs, fmax, ncs, groups) < 0)
             return ate_fail(ctx, -1, "irls_round: a column list exceeds the tile plan");
     }
     if (groups.empty()) {
