@@ -49,7 +49,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if (not force and os.path.exists(obj)
                 and os.path.getmtime(obj) > max(os.path.getmtime(f) for f in [src] + hdrs)):
             continue
-        extra = os.environ.get("ATE_EXTRA_NVCC_FLAGS", "").split()  # e.g. -DATE_STEP_TRACE for tools/step_trace.py
+        extra = os.environ.get("ATE_EXTRA_NVCC_FLAGS", "").split()  # e.g. -DATE_ROUND_TRACE (tools/round_trace.py); tools/build_variant_lib.sh builds A/B variants beside the library
         cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
