@@ -409,11 +409,46 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     const int nlead = P, nfol = P * F, nfits = nlead + nfol;
     const size_t m2 = (size_t)mS * mS;
 
+    // ---- device state: one block cached in the ctx, carved (a second call of the same shape allocates
+    //      nothing: with one process per GPU, cudaMalloc / cudaFree of eight processes serialise in the
+    //      driver and showed up as tens of ms of the outcome stage at 8 GPUs) ----
+    const size_t n2 = (size_t)ni * ni;
+    struct Ptr { double *p; };
+    struct IPtr { int *p; };
+    Ptr dSf{nullptr}, dStot{nullptr}, dC{nullptr}, dvec{nullptr}, dout{nullptr}, dvp{nullptr}, dulam{nullptr}, dcv{nullptr};
+    IPtr dint{nullptr}, dnl{nullptr};
+    struct { GaussFit *p; } dfits{nullptr};
+    {
+        char *base = nullptr;
+        for (int pass = 0; pass < 2; ++pass) {
+            size_t off = 0;
+            auto take = [&](size_t bytes) {
+                off = (off + 255) / 256 * 256;
+                char *q = base ? base + off : nullptr;
+                off += bytes ? bytes : 8;
+                return q;
+            };
+            dStot.p = (double *)take(sizeof(double) * m2 * P);
+            dSf.p = (double *)take(sizeof(double) * m2 * (size_t)(F > 0 ? nfol : 0));
+            dC.p = (double *)take(sizeof(double) * n2 * nfits);
+            dvec.p = (double *)take(sizeof(double) * (size_t)nfits * (3 * (size_t)ni + 4));                       // g, xm, xs, scal
+            dout.p = (double *)take(sizeof(double) * (size_t)nfits * (3 * (size_t)nlam + (size_t)ni * nlam));     // alm, rsq, a0, beta
+            dvp.p = (double *)take(sizeof(double) * ni);
+            dulam.p = (double *)take(sizeof(double) * nlam);
+            dcv.p = (double *)take(sizeof(double) * (size_t)(F > 0 ? nfol : 0) * nlam);
+            dint.p = (int *)take(sizeof(int) * (size_t)nfits * ((size_t)ni + 4));                                 // ju, lmu, nlp, jerr
+            dnl.p = (int *)take(sizeof(int));
+            dfits.p = (GaussFit *)take(sizeof(GaussFit) * nfits);
+            if (pass == 0) {
+                void *blk = nullptr;
+                ATE_TRY(ate_cached(ctx, "gauss.state", off + 256, &blk));
+                base = (char *)blk;
+            }
+        }
+    }
+
     // ---- moment matrices: one Gram per (problem, inner fold), then totals ----
-    DevBuf<double> dSf, dStot;
-    ATE_CUDA(ctx, dStot.alloc(m2 * P));
     if (F > 0) {
-        ATE_CUDA(ctx, dSf.alloc(m2 * (size_t)nfol));
         for (int p = 0; p < P; ++p)
             for (int f = 0; f < F; ++f)
                 ATE_TRY(ate_i_gram(ctx, X, ld, mS, probs[p].d_list, probs[p].seg[f],
@@ -432,23 +467,8 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     }
 
     // ---- per-fit workspace and outputs ----
-    const size_t n2 = (size_t)ni * ni;
-    DevBuf<double> dC, dvec, dout, dvp, dulam, dcv;
-    DevBuf<int> dint;
-    DevBuf<GaussFit> dfits;
-    ATE_CUDA(ctx, dC.alloc(n2 * nfits));
-    ATE_CUDA(ctx, dvec.alloc((size_t)nfits * (3 * (size_t)ni + 4)));           // g, xm, xs, scal
-    ATE_CUDA(ctx, dout.alloc((size_t)nfits * (3 * (size_t)nlam + (size_t)ni * nlam)));  // alm, rsq, a0, beta
-    ATE_CUDA(ctx, dint.alloc((size_t)nfits * ((size_t)ni + 4)));               // ju, lmu, nlp, jerr
-    ATE_CUDA(ctx, dfits.alloc(nfits));
-    if (vp_host) {
-        ATE_CUDA(ctx, dvp.alloc(ni));
-        ATE_CUDA(ctx, cudaMemcpyAsync(dvp.p, vp_host, sizeof(double) * ni, cudaMemcpyHostToDevice, ctx->stream));
-    }
-    if (po.flmin >= 1.0) {
-        ATE_CUDA(ctx, dulam.alloc(nlam));
-        ATE_CUDA(ctx, cudaMemcpyAsync(dulam.p, po.ulam, sizeof(double) * nlam, cudaMemcpyHostToDevice, ctx->stream));
-    }
+    if (vp_host) ATE_CUDA(ctx, cudaMemcpyAsync(dvp.p, vp_host, sizeof(double) * ni, cudaMemcpyHostToDevice, ctx->stream));
+    if (po.flmin >= 1.0) ATE_CUDA(ctx, cudaMemcpyAsync(dulam.p, po.ulam, sizeof(double) * nlam, cudaMemcpyHostToDevice, ctx->stream));
     std::vector<GaussFit> hf(nfits);
     auto fill = [&](int id, const double *St, const double *Ss) {
         GaussFit &g = hf[id];
@@ -483,9 +503,7 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             hf[id].nlam_ptr = hf[p].lmu;
         }
     // leaders with user lambdas need a device count too
-    DevBuf<int> dnl;
     if (po.flmin >= 1.0) {
-        ATE_CUDA(ctx, dnl.alloc(1));
         ATE_CUDA(ctx, cudaMemcpyAsync(dnl.p, &nlam, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
         for (int p = 0; p < P; ++p) hf[p].nlam_ptr = dnl.p;
     }
@@ -503,7 +521,6 @@ int ate_i_cv_gaussian(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     if (F > 0) {
         gauss_path_kernel<<<nfol, PATH_THREADS, path_smem, ctx->stream>>>(dfits.p + nlead);
         ATE_LAUNCHED(ctx);
-        ATE_CUDA(ctx, dcv.alloc((size_t)nfol * nlam));
         gauss_cv_kernel<<<dim3(nfol, nlam), 128, 0, ctx->stream>>>(dfits.p, nlead, nlam, dcv.p);
         ATE_LAUNCHED(ctx);
     }
