@@ -136,6 +136,10 @@ for k in range(K):
         mine[k] = want[k]
 rc = eng._allreduce_cb(None, mine.ctypes.data_as(C.POINTER(C.c_double)), mine.size)
 assert rc == 0 and np.array_equal(mine, want), mine
+# 4. the 128-byte NCCL id travels from rank 0 to every rank unchanged (parallel.init_nccl)
+ident = bytes((7 * i + 3) % 256 for i in range(128))
+got_id = comm.broadcast_bytes(ident if comm.rank == 0 else None, 128)
+assert got_id == ident, got_id
 dist.destroy_process_group()
 print("ok", comm.rank)
 """

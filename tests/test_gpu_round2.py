@@ -134,3 +134,35 @@ def test_crossfit_draws_identical_folds_on_identical_calls(engine):
     assert a["tau"] == b["tau"] and np.array_equal(a["lambda_ps"], b["lambda_ps"])
     fo = engine.r_foldid(10, 5)     # and the stream the user sees is untouched in kind
     assert fo.min() == 1 and fo.max() == 5
+
+
+def test_fold_fits_joining_their_full_data_fit_change_nothing(engine):
+    """The cv-fold fits of a binomial cv.glmnet start as soon as their full-data fit has fixed the lambda
+    sequence (three lambdas recorded) instead of after it has finished (ATE_TWO_PHASE=1, the order R runs
+    them in): same lambdas, same fold errors, same coefficients, bit for bit -- a fit's iterates depend on
+    its own sums only."""
+    from test_gpu_wide_binomial import unique_product_design
+    n, p = 12_000, 120
+    X, y = unique_product_design(n, p, seed=21)
+    fid = synth.fold_ids(n, 10, 4)
+    # the switch is read once per process: run the sequential order in a child process
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "from ate_replication_causalml_b200.engine import Engine\n"
+        "d = np.load(sys.argv[1]); eng = Engine(0)\n"
+        "g = eng.cv_glmnet(np.asfortranarray(d['X']), d['y'], 'binomial', foldid=d['fid'])\n"
+        "np.savez(sys.argv[2], cvm=g['cvm'], cvsd=g['cvsd'], beta=g['beta'], a0=g['a0'], lam=g['lambda_'], idx=np.array([g['idx_min'], g['idx_1se'], g['lmu']]))\n"
+    ) % (ROOT, os.path.join(ROOT, "tests"))
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        inp, out = os.path.join(td, "in.npz"), os.path.join(td, "out.npz")
+        np.savez(inp, X=X, y=y, fid=fid)
+        env = dict(os.environ, ATE_TWO_PHASE="1")
+        r = subprocess.run([sys.executable, "-c", code, inp, out], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        seq = np.load(out)
+        g = engine.cv_glmnet(X, y, "binomial", foldid=fid)
+        assert [g["idx_min"], g["idx_1se"], g["lmu"]] == list(seq["idx"])
+        assert np.array_equal(g["lambda_"], seq["lam"])
+        assert np.array_equal(g["cvm"], seq["cvm"]) and np.array_equal(g["cvsd"], seq["cvsd"])
+        assert np.array_equal(g["beta"], seq["beta"]) and np.array_equal(g["a0"], seq["a0"])
