@@ -37,7 +37,7 @@ namespace {
 
 enum { PH_INIT = 0, PH_REFRESH = 1 };
 enum { SD_B0 = 0, SD_BS0, SD_AL, SD_AL0, SD_DEV0, SD_DEV1, SD_SHR, SD_ALF, SD_Q0, SD_BZ, SD_SUMS, SD_SUMS2, SD_SUMA, SD_N };
-enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_NG, SI_RETRY, SI_MISS, SI_ONES, SI_N };
+enum { SI_NIN = 0, SI_ILM, SI_PHASE, SI_DONE, SI_NLP, SI_JERR, SI_LMU, SI_ROUNDS, SI_NS, SI_SOLVE, SI_NG, SI_RETRY, SI_MISS, SI_ONES, SI_NEWLIST, SI_N };
 // sums layout: gr[ni] = X^T r, hx[ni] = X^T v, hxx[ni] = sum v x^2, then XMZ, SR, DEV
 enum { SU_XMZ = 0, SU_SR, SU_DEV, SU_N };
 
@@ -60,7 +60,7 @@ struct LognetFit {
     int maxit;
     double *coef;     // ni + 1 (a0 last): raw-scale coefficients for the next eval
     double *st_d;     // b, bs, xv, ga, xm, xs, vq [7 ni] + SD_N
-    int *st_i;        // ixx, mm, mlist, ju, spos, gpos [6 ni] + slist [ldh] + glist [ldh] + SI_N
+    int *st_i;        // ixx, mm, mlist, ju, spos, gpos [6 ni] + slist [ldh] + glist [ldh] + SI_N + next glist [ldh] + next gpos [ni]
     double *alm, *a0, *dev, *beta;  // outputs
 };
 
@@ -83,6 +83,17 @@ __device__ __forceinline__ int fit_nlam(const LognetFit &f) {
 __device__ __forceinline__ int *fit_slist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni; }
 __device__ __forceinline__ int *fit_glist(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + f.ldh; }
 __device__ __forceinline__ int *fit_scal_i(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + 2 * (size_t)f.ldh; }
+// the list the NEXT step will use (built by lognet_pre_kernel while this step's H is still in use; copied over
+// glist / gpos by lognet_solve_kernel when it is through with H)
+__device__ __forceinline__ int *fit_glist_next(const LognetFit &f) { return f.st_i + 6 * (size_t)f.ni + 2 * (size_t)f.ldh + SI_N; }
+__device__ __forceinline__ int *fit_gpos_next(const LognetFit &f) { return fit_glist_next(f) + f.ldh; }
+__device__ __forceinline__ void fit_write_flags(const LognetFit &f, int *flags_out) {
+    const int *si = f.st_i + 6 * (size_t)f.ni + 2 * (size_t)f.ldh;
+    flags_out[4 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
+    flags_out[4 * blockIdx.x + 1] = si[SI_DONE] ? 0 : si[SI_NG];
+    flags_out[4 * blockIdx.x + 2] = si[SI_LMU];
+    flags_out[4 * blockIdx.x + 3] = si[SI_ONES];
+}
 __device__ __forceinline__ double *fit_scal_d(const LognetFit &f) { return f.st_d + 7 * (size_t)f.ni; }
 
 // one warp per output element, partials folded in a fixed (lane-strided, then butterfly) order
@@ -179,16 +190,20 @@ __device__ __forceinline__ double bmax_all(double v, double *red) {
 // strong-set update.  The step computed H over last round's prediction of the strong set; when a
 // column joined that the prediction missed, SI_RETRY is raised: the solve kernel then only rebuilds
 // the list (around the exact strong set), the step repeats at the same coefficients, and the next
-// visit here goes straight to the solve.
+// visit here goes straight to the solve.  flags_out[4 fit + {0, 1, 2, 3}] = {done, length of the next list,
+// lambdas recorded, position of the ONE column in that list or -1}: what the host needs to plan the next launch.
 __global__ void __launch_bounds__(CD_THREADS)
-lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev) {
+lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev, int *__restrict__ flags_out) {
     const LognetFit f = fits[blockIdx.x];
     const RoundDev rd = rdev[blockIdx.x];
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
     if (si[SI_DONE] || !rd.live) {
-        if (tid == 0) si[SI_SOLVE] = 0;
+        if (tid == 0) {
+            si[SI_SOLVE] = 0;
+            fit_write_flags(f, flags_out);
+        }
         return;
     }
     if (f.lead_done && *f.lead_done && si[SI_ILM] >= *f.nlam_ptr && si[SI_PHASE] != PH_INIT) {
@@ -196,15 +211,20 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
         if (tid == 0) {
             si[SI_DONE] = 1;
             si[SI_SOLVE] = 0;
+            fit_write_flags(f, flags_out);
         }
         return;
     }
     if (si[SI_RETRY]) {  // the bookkeeping of this step was done last round; H now covers the strong set
-        if (tid == 0) si[SI_RETRY] = 0;
+        if (tid == 0) {
+            si[SI_RETRY] = 0;
+            fit_write_flags(f, flags_out);  // the next step keeps the list (the strong set has not changed)
+        }
         return;
     }
     extern __shared__ double sm[];
     double *g = sm, *red = g + ni;  // red[32]
+    int *cand = reinterpret_cast<int *>(red + 32), *srt = cand + f.ldh;  // scratch of the list builder
     double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gga = Gxv + ni, *Gxm = Gga + ni,
            *Gxs = Gxm + ni, *Gvq = Gxs + ni;
     int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni, *Ggpos = Gspos + ni;
@@ -397,30 +417,94 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
                 for (int k = 0; k < si[SI_LMU]; ++k) f.seq[k] = f.alm[k];
         }
     }
+    __syncthreads();
+    if (finished) {
+        if (tid == 0) fit_write_flags(f, flags_out);
+        return;
+    }
+    // ---- column list of the NEXT fused step: the strong set, then the likely joiners -- every column whose
+    //      gradient is within 10 % of the next strong-rule / KKT threshold.  It depends on what this kernel has
+    //      just decided (strong set, lambda) and on the gradient the round started from, not on the solve:
+    //      built here, its length reaches the host while the solve still runs, and the host plans the next
+    //      launch in that time.  The list goes to the `next` arrays: this round's H is indexed by the current
+    //      ones until lognet_solve_kernel is through with it. ----
+    double tnext;
+    {
+        const int nlam_n = fit_nlam(f);
+        double aln;
+        if (f.flmin >= 1.0)
+            aln = (ilm + 1 < nlam_n) ? f.ulam[ilm + 1] : al;
+        else if (ilm == 0) {
+            double t = 0.0;
+            for (int j = tid; j < ni; j += T)
+                if (Gju[j] && Gvq[j] > 0.0) t = fmax(t, fabs(g[j]) / Gvq[j]);
+            aln = alf * bmax_all(t, red);
+        } else
+            aln = al * alf;
+        const double cur = (ilm == 0 && f.flmin < 1.0) ? aln / alf : al;  // lambda_1 = "big" has no meaning here
+        tnext = 0.9 * fmin(2.0 * aln - cur, cur);
+        if (!(tnext > 0.0)) tnext = 0.0;
+    }
+    int *glist = fit_glist_next(f), *gpos = fit_gpos_next(f);
+    for (int j = tid; j < ni; j += T) gpos[j] = -1;
+    __syncthreads();
+    if (tid == 0) {
+        int nG = 0;
+        for (int c = 0; c < nS; ++c) cand[nG++] = slist[c];
+        for (int k = 0; k < ni && nG < f.ldh; ++k)
+            if (!Gixx[k] && Gju[k] && fabs(g[k]) > tnext * Gvq[k]) cand[nG++] = k;
+        // Order of the list.  An MMA warp loads, per 8x8 tile, 8 list columns x 4 staged rows; consecutive
+        // rows sit 12 (mod 16) doubles apart, so four columns x four rows hit the 16 eight-byte banks once
+        // each exactly when the four columns have four different residues mod 4 (a 64-bit shared load is
+        // served half a warp at a time: class order 0 1 2 3 0 1 2 3, not 0 0 1 1 2 2 3 3, which cost 40 % extra
+        // wavefronts in the C1 capture).  Deal the columns into such groups of four while all four classes
+        // last; the classes that are left still take turns.
+        int cnt4[4] = {0, 0, 0, 0}, beg4[4], pos4[4];
+        for (int c = 0; c < nG; ++c) cnt4[cand[c] & 3]++;
+        beg4[0] = 0;
+        for (int q = 1; q < 4; ++q) beg4[q] = beg4[q - 1] + cnt4[q - 1];
+        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
+        for (int c = 0; c < nG; ++c) srt[pos4[cand[c] & 3]++] = cand[c];
+        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
+        int out = 0;
+        for (bool any = true; any;) {
+            any = false;
+            for (int q = 0; q < 4; ++q)
+                if (cnt4[q] > 0) {
+                    glist[out++] = srt[pos4[q]++];
+                    --cnt4[q];
+                    any = true;
+                }
+        }
+        for (int c = 0; c < nG; ++c) gpos[glist[c]] = c;
+        // A wide list gets a CTA of its own in the step kernel, whose helpers are its slowest warps: such a
+        // list ends with the staged rows' ONE column, the Gram's row of that column IS X^T v of the list
+        // columns (all the solve reads of it), and the helpers compute X^T r only.
+        int ones = -1;
+        if (nG + 1 >= R_ONES_MIN && nG < f.ldh) {
+            ones = nG;
+            glist[nG++] = f.ncs + 1;
+        }
+        const int npad = (nG + 31) / 32 * 32;
+        for (int c = nG; c < npad && c < f.ldh; ++c) glist[c] = f.ncs;
+        si[SI_NG] = nG;
+        si[SI_ONES] = ones;
+        si[SI_NEWLIST] = 1;
+        fit_write_flags(f, flags_out);
+    }
 }
 
 // ---- IRLS round, part 2: solve the penalised quadratic on the strong set -------------------
-// H holds X_L^T V X_L over the column list L the step used (positions gpos).  At the end the list for
-// the next step is rebuilt: the strong set plus every column whose gradient is within 10 % of the
-// next strong-rule / KKT threshold, ordered so that the MMA warps' gathered operand loads spread over
-// the shared-memory banks.  flags_out[4 fit + {0, 1, 2, 3}] = {done, length of the next list, lambdas recorded, position of the
-// ONE column in that list or -1}.
+// H holds X_L^T V X_L over the column list L the step used (positions gpos).  At the end the list
+// lognet_pre_kernel built for the next step replaces L.
 __global__ void __launch_bounds__(CD_THREADS)
-lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev, int *__restrict__ flags_out) {
+lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev) {
     const LognetFit f = fits[blockIdx.x];
     const RoundDev rd = rdev[blockIdx.x];
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x, ldh = rd.ldh;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
-    if (si[SI_DONE] || !si[SI_SOLVE] || !rd.live) {
-        if (tid == 0) {
-            flags_out[4 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
-            flags_out[4 * blockIdx.x + 1] = si[SI_DONE] ? 0 : si[SI_NG];
-            flags_out[4 * blockIdx.x + 2] = si[SI_LMU];
-            flags_out[4 * blockIdx.x + 3] = si[SI_ONES];
-        }
-        return;
-    }
+    if (si[SI_DONE] || !si[SI_SOLVE] || !rd.live) return;
     const bool retry = si[SI_RETRY] != 0;  // list rebuild only: H does not cover the strong set yet
     extern __shared__ double sm[];
     double *b = sm, *g = b + ni, *hxs = g + ni, *xv = hxs + ni, *vq = xv + ni, *red = vq + ni;  // red[32]
@@ -577,77 +661,16 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
             Gml[j] = ml[j];
         }
     const double dotbm = bsum_all(part, red);
-    // ---- column list of the next fused step: the strong set, then the likely joiners.  g[] of a
-    //      non-strong column is still the gradient this round started from. ----
-    double tnext;
-    {
-        const int nlam = fit_nlam(f);
-        const double alf = sd[SD_ALF];
-        double aln;
-        if (f.flmin >= 1.0)
-            aln = (ilm + 1 < nlam) ? f.ulam[ilm + 1] : al1;
-        else if (ilm == 0) {
-            double t = 0.0;
-            for (int j = tid; j < ni; j += T)
-                if (Gju[j] && vq[j] > 0.0) t = fmax(t, fabs(g[j]) / vq[j]);
-            aln = alf * bmax_all(t, red);
-        } else
-            aln = al1 * alf;
-        const double cur = (ilm == 0 && f.flmin < 1.0) ? aln / alf : al1;  // lambda_1 = "big" has no meaning here
-        tnext = 0.9 * fmin(2.0 * aln - cur, cur);
-        if (!(tnext > 0.0)) tnext = 0.0;
+    // ---- this round's H is done with: the list lognet_pre_kernel built for the next step becomes current ----
+    __syncthreads();
+    if (si[SI_NEWLIST]) {
+        const int *gn = fit_glist_next(f), *pn = fit_gpos_next(f);
+        for (int c = tid; c < f.ldh; c += T) glist[c] = gn[c];
+        for (int j = tid; j < ni; j += T) Ggpos[j] = pn[j];
     }
-    for (int j = tid; j < ni; j += T) Ggpos[j] = -1;
     __syncthreads();
     if (tid == 0) {
-        int nG = 0;
-        for (int c = 0; c < nS; ++c) cand[nG++] = sl[c];
-        for (int k = 0; k < ni && nG < f.ldh; ++k)
-            if (!ixx[k] && Gju[k] && fabs(g[k]) > tnext * vq[k]) cand[nG++] = k;
-        // Order of the list.  An MMA warp loads, per 8x8 tile, 8 list columns x 4 staged rows; consecutive
-        // rows sit 12 (mod 16) doubles apart, so four columns x four rows hit the 16 eight-byte banks once
-        // each exactly when the four columns have four different residues mod 4.  Deal the columns into
-        // such groups of four while all four classes last.
-        int cnt4[4] = {0, 0, 0, 0}, beg4[4], pos4[4];
-        for (int c = 0; c < nG; ++c) cnt4[cand[c] & 3]++;
-        beg4[0] = 0;
-        for (int q = 1; q < 4; ++q) beg4[q] = beg4[q - 1] + cnt4[q - 1];
-        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
-        for (int c = 0; c < nG; ++c) srt[pos4[cand[c] & 3]++] = cand[c];
-        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
-        int out = 0;
-        // (a 64-bit shared load is served half a warp at a time, i.e. FOUR consecutive list columns x four
-        // rows: every aligned group of four must hold all four classes -- class order 0 1 2 3 0 1 2 3, not
-        // 0 0 1 1 2 2 3 3, which cost 40 % extra wavefronts in the C1 capture)
-        while (cnt4[0] >= 1 && cnt4[1] >= 1 && cnt4[2] >= 1 && cnt4[3] >= 1)
-            for (int q = 0; q < 4; ++q) {
-                glist[out++] = srt[pos4[q]++];
-                cnt4[q] -= 1;
-            }
-        for (bool any = true; any;) {  // the remainder: the classes that are left, still taking turns
-            any = false;
-            for (int q = 0; q < 4; ++q)
-                if (cnt4[q] > 0) {
-                    glist[out++] = srt[pos4[q]++];
-                    --cnt4[q];
-                    any = true;
-                }
-        }
-        for (int c = 0; c < nG; ++c) Ggpos[glist[c]] = c;
-        // A wide list gets a CTA of its own in the step kernel, whose helpers are its slowest warps: such a
-        // list ends with the staged rows' ONE column, the Gram's row of that column IS X^T v of the list
-        // columns (all the solve reads of it), and the helpers compute X^T r only.
-        int ones = -1;
-        if (nG + 1 >= R_ONES_MIN && nG < f.ldh) {
-            ones = nG;
-            glist[nG++] = f.ncs + 1;
-        }
-        const int npad = (nG + 31) / 32 * 32;
-        for (int c = nG; c < npad && c < f.ldh; ++c) glist[c] = f.ncs;
-        si[SI_NG] = nG;
-        si[SI_ONES] = ones;
-        flags_out[4 * blockIdx.x + 1] = nG;
-        flags_out[4 * blockIdx.x + 3] = ones;
+        si[SI_NEWLIST] = 0;
         if (!retry) {
             f.coef[ni] = b0 - dotbm;
             sd[SD_B0] = b0;
@@ -656,11 +679,9 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
             si[SI_ROUNDS] += 1;
             if (fail) {
                 si[SI_JERR] = -(ilm + 1);
-                si[SI_DONE] = 1;
+                si[SI_DONE] = 1;  // (the host reads it from lognet_pre_kernel's flags of the next round)
             }
         }
-        flags_out[4 * blockIdx.x] = si[SI_DONE] ? 1 : 0;
-        flags_out[4 * blockIdx.x + 2] = si[SI_LMU];
     }
 }
 
@@ -850,7 +871,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     // the step kernel stages [0, ncs) of every row: the features and the response column
     const int ncs = ((ni > iy ? ni : iy) + 1 + 7) / 8 * 8;
     if (ldh > ld || ncs > ld) return ate_fail(ctx, -1, "cv_binomial: design ld (%lld) too small for %d features", ld, ni);
-    const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 6 * (size_t)ni + 2 * (size_t)ldh + SI_N;
+    const size_t sd_len = 7 * (size_t)ni + SD_N, si_len = 7 * (size_t)ni + 3 * (size_t)ldh + SI_N;
     const size_t si_scal = 6 * (size_t)ni + 2 * (size_t)ldh;
     const size_t out_len = 3 * (size_t)nlam + (size_t)ni * nlam;
     const int ev_blocks = ctx->num_sms * 2;
@@ -984,7 +1005,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     lognet_init_kernel<<<nfits, 256, 0, ctx->stream>>>(dfits, dysum, nsegp);
     ATE_LAUNCHED(ctx);
 
-    const size_t pre_smem = sizeof(double) * ((size_t)ni + 32);
+    const size_t pre_smem = sizeof(double) * ((size_t)ni + 32) + sizeof(int) * 2 * (size_t)ldh;
     const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * (4 * (size_t)ni + 3 * (size_t)ldh);
     if (cd_smem > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
     if (cd_smem > 48 * 1024)
@@ -1003,6 +1024,12 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     RoundDev *hrdev = (RoundDev *)hrdev_v;
     std::vector<RoundFit> rfits(nfits);
     std::vector<RoundSlot> slots;
+    struct EventGuard {
+        cudaEvent_t e = nullptr;
+        ~EventGuard() { if (e) cudaEventDestroy(e); }
+    } evg;
+    ATE_CUDA(ctx, cudaEventCreateWithFlags(&evg.e, cudaEventDisableTiming));
+    cudaEvent_t ev_flags = evg.e;
     int rounds = 0;
     const int max_rounds = nlam * 60 + 100;
     RoundStats rst;
@@ -1069,17 +1096,20 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         ATE_CUDA(ctx, cudaMemcpyAsync(drdev, hrdev, sizeof(RoundDev) * nfits, cudaMemcpyHostToDevice, ctx->stream));
         // the full-data fits first: what they record this round (lmu, done, the sequence) is what their
         // fold fits read in the second launch
-        lognet_pre_kernel<<<nlead, CD_THREADS, pre_smem, ctx->stream>>>(dfits, drdev);
+        lognet_pre_kernel<<<nlead, CD_THREADS, pre_smem, ctx->stream>>>(dfits, drdev, dflags);
         ATE_LAUNCHED(ctx);
         if (nfol > 0) {
-            lognet_pre_kernel<<<nfol, CD_THREADS, pre_smem, ctx->stream>>>(dfits + nlead, drdev + nlead);
+            lognet_pre_kernel<<<nfol, CD_THREADS, pre_smem, ctx->stream>>>(dfits + nlead, drdev + nlead, dflags + 4 * (size_t)nlead);
             ATE_LAUNCHED(ctx);
         }
-        lognet_solve_kernel<<<nfits, CD_THREADS, cd_smem, ctx->stream>>>(dfits, drdev, dflags);
-        ATE_LAUNCHED(ctx);
+        // what the host needs for the next launch (who is done, how long the next lists are) is known now: it
+        // is read back while the solve runs, and the next round is planned and enqueued behind the solve
         ATE_CUDA(ctx, cudaMemcpyAsync(hflags, dflags, sizeof(int) * 4 * nfits, cudaMemcpyDeviceToHost, ctx->stream));
+        ATE_CUDA(ctx, cudaEventRecord(ev_flags, ctx->stream));
+        lognet_solve_kernel<<<nfits, CD_THREADS, cd_smem, ctx->stream>>>(dfits, drdev);
+        ATE_LAUNCHED(ctx);
         if (timing) { const double t = tnow(); t_host += t - t_mark; t_mark = t; }
-        ATE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        ATE_CUDA(ctx, cudaEventSynchronize(ev_flags));
         if (timing) { const double t = tnow(); t_wait += t - t_mark; t_mark = t; }
         for (int id = 0; id < nfits; ++id) {
             if (!rfits[id].live) continue;
