@@ -979,7 +979,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
             g.seq = dseq + (size_t)nlam * id;
         } else {
             g.flmin = 1.0;
-            g.ulam = hf[p].seq;
+            g.ulam = po.flmin >= 1.0 ? dulam : hf[p].seq;  // the caller's sequence, or the one the full-data fit publishes
             g.nlam_ptr = hf[p].st_i + si_scal + SI_LMU;
             g.lead_done = hf[p].st_i + si_scal + SI_DONE;
             g.seq = nullptr;
