@@ -13,7 +13,9 @@
 //                        the flops).  If a column joined that the step's list missed (rare: the
 //                        list carries a 10 % margin), the solve is put off by one round: the list
 //                        is rebuilt around the exact strong set and the step repeats at the same
-//                        coefficients -- no host decision is involved.
+//                        coefficients -- no host decision is involved.  Last, the column list of
+//                        the NEXT step is built (strong set + columns within 10 % of the next
+//                        threshold): the host reads its length while the solve still runs.
 //   lognet_solve_kernel: one CTA per fit.  Standardises the compact H in place (lstandard1's
 //                        centring and 1/N scaling are affine in H, X^T v, sum v), then follows
 //                        lognet2n's loop order exactly -- strong-set sweep, intercept step,
