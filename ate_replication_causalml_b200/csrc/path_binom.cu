@@ -31,8 +31,10 @@
 #include <stdlib.h>
 
 #include <chrono>
+#include <type_traits>
 
 #include "irls_round.cuh"
+#include "tma_dmma.cuh"
 #include "path.cuh"
 
 namespace {
@@ -201,14 +203,19 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x;
     int *si = fit_scal_i(f);
     double *sd = fit_scal_d(f);
-    if (si[SI_DONE] || !rd.live) {
+    // every thread reads the state these early exits depend on BEFORE thread 0 changes any of it (a warp that
+    // read SI_RETRY after thread 0 had cleared it would run the bookkeeping below on its own)
+    const bool st_done = si[SI_DONE] != 0, st_retry = si[SI_RETRY] != 0;
+    const bool st_lead_stop = f.lead_done && *f.lead_done && si[SI_ILM] >= *f.nlam_ptr && si[SI_PHASE] != PH_INIT;
+    __syncthreads();
+    if (st_done || !rd.live) {
         if (tid == 0) {
             si[SI_SOLVE] = 0;
             fit_write_flags(f, flags_out);
         }
         return;
     }
-    if (f.lead_done && *f.lead_done && si[SI_ILM] >= *f.nlam_ptr && si[SI_PHASE] != PH_INIT) {
+    if (st_lead_stop) {
         // a cv-fold fit that ran ahead of its full-data fit, which has now stopped short of this lambda
         if (tid == 0) {
             si[SI_DONE] = 1;
@@ -217,7 +224,7 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
         }
         return;
     }
-    if (si[SI_RETRY]) {  // the bookkeeping of this step was done last round; H now covers the strong set
+    if (st_retry) {  // the bookkeeping of this step was done last round; H now covers the strong set
         if (tid == 0) {
             si[SI_RETRY] = 0;
             fit_write_flags(f, flags_out);  // the next step keeps the list (the strong set has not changed)
@@ -449,46 +456,65 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
     }
     int *glist = fit_glist_next(f), *gpos = fit_gpos_next(f);
     for (int j = tid; j < ni; j += T) gpos[j] = -1;
+    nS = si[SI_NS];  // thread 0 appended the newly strong columns above (its copy alone was current)
     __syncthreads();
-    if (tid == 0) {
-        int nG = 0;
-        for (int c = 0; c < nS; ++c) cand[nG++] = slist[c];
-        for (int k = 0; k < ni && nG < f.ldh; ++k)
-            if (!Gixx[k] && Gju[k] && fabs(g[k]) > tnext * Gvq[k]) cand[nG++] = k;
+    if (tid < 32) {
+        // one warp builds the list (a single thread took ~50 us per launch, all of it on the round's
+        // critical path): ordered compaction by ballot, then every element computes its own position
+        const int lane = tid;
+        const unsigned lt = (1u << lane) - 1u;
+        int nG = nS < f.ldh ? nS : f.ldh;
+        for (int c = lane; c < nG; c += 32) cand[c] = slist[c];
+        for (int k0 = 0; k0 < ni; k0 += 32) {  // the joiners, in ascending column order
+            const int k = k0 + lane;
+            const bool take = k < ni && !Gixx[k] && Gju[k] && fabs(g[k]) > tnext * Gvq[k];
+            const unsigned m = __ballot_sync(0xffffffffu, take);
+            const int at = nG + __popc(m & lt);
+            if (take && at < f.ldh) cand[at] = k;
+            nG = min(f.ldh, nG + __popc(m));
+        }
+        __syncwarp();
         // Order of the list.  An MMA warp loads, per 8x8 tile, 8 list columns x 4 staged rows; consecutive
         // rows sit 12 (mod 16) doubles apart, so four columns x four rows hit the 16 eight-byte banks once
         // each exactly when the four columns have four different residues mod 4 (a 64-bit shared load is
         // served half a warp at a time: class order 0 1 2 3 0 1 2 3, not 0 0 1 1 2 2 3 3, which cost 40 % extra
-        // wavefronts in the C1 capture).  Deal the columns into such groups of four while all four classes
-        // last; the classes that are left still take turns.
-        int cnt4[4] = {0, 0, 0, 0}, beg4[4], pos4[4];
-        for (int c = 0; c < nG; ++c) cnt4[cand[c] & 3]++;
-        beg4[0] = 0;
-        for (int q = 1; q < 4; ++q) beg4[q] = beg4[q - 1] + cnt4[q - 1];
-        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
-        for (int c = 0; c < nG; ++c) srt[pos4[cand[c] & 3]++] = cand[c];
-        for (int q = 0; q < 4; ++q) pos4[q] = beg4[q];
-        int out = 0;
-        for (bool any = true; any;) {
-            any = false;
-            for (int q = 0; q < 4; ++q)
-                if (cnt4[q] > 0) {
-                    glist[out++] = srt[pos4[q]++];
-                    --cnt4[q];
-                    any = true;
-                }
+        // wavefronts in the C1 capture).  The classes take turns while they last: the r-th column of class q
+        // (in the order above) goes to position sum_q' min(cnt[q'], r) + #{q' < q : cnt[q'] > r}.
+        int run[4] = {0, 0, 0, 0};
+        for (int c0 = 0; c0 < nG; c0 += 32) {
+            const int c = c0 + lane;
+            const int q = c < nG ? (cand[c] & 3) : -1;
+            int r = 0;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+                const unsigned m = __ballot_sync(0xffffffffu, q == qq);
+                if (q == qq) r = run[qq] + __popc(m & lt);
+                run[qq] += __popc(m);
+            }
+            if (c < nG) srt[c] = r;
         }
-        for (int c = 0; c < nG; ++c) gpos[glist[c]] = c;
+        __syncwarp();
+        for (int c = lane; c < nG; c += 32) {
+            const int k = cand[c], q = k & 3, r = srt[c];
+            int at = 0;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) at += min(run[qq], r) + ((qq < q && run[qq] > r) ? 1 : 0);
+            glist[at] = k;
+            gpos[k] = at;
+        }
         // A wide list gets a CTA of its own in the step kernel, whose helpers are its slowest warps: such a
         // list ends with the staged rows' ONE column, the Gram's row of that column IS X^T v of the list
         // columns (all the solve reads of it), and the helpers compute X^T r only.
         int ones = -1;
         if (nG + 1 >= R_ONES_MIN && nG < f.ldh) {
             ones = nG;
-            glist[nG++] = f.ncs + 1;
+            if (lane == 0) glist[nG] = f.ncs + 1;
+            ++nG;
         }
         const int npad = (nG + 31) / 32 * 32;
-        for (int c = nG; c < npad && c < f.ldh; ++c) glist[c] = f.ncs;
+        for (int c = nG + lane; c < npad && c < f.ldh; c += 32) glist[c] = f.ncs;
+        __syncwarp();
+        if (lane != 0) return;
         si[SI_NG] = nG;
         si[SI_ONES] = ones;
         si[SI_NEWLIST] = 1;
@@ -500,7 +526,7 @@ lognet_pre_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict
 // H holds X_L^T V X_L over the column list L the step used (positions gpos).  At the end the list
 // lognet_pre_kernel built for the next step replaces L.
 __global__ void __launch_bounds__(CD_THREADS)
-lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev) {
+lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restrict__ rdev, int hs_cap) {
     const LognetFit f = fits[blockIdx.x];
     const RoundDev rd = rdev[blockIdx.x];
     const int ni = f.ni, tid = threadIdx.x, T = blockDim.x, ldh = rd.ldh;
@@ -511,7 +537,10 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
     extern __shared__ double sm[];
     double *b = sm, *g = b + ni, *hxs = g + ni, *xv = hxs + ni, *vq = xv + ni, *red = vq + ni;  // red[32]
     int *ixx = reinterpret_cast<int *>(red + 32), *mm = ixx + ni, *ml = mm + ni, *hp = ml + ni,
-        *sl = hp + ni, *cand = sl + f.ldh, *srt = cand + f.ldh;
+        *sl = hp + ni, *spos = sl + f.ldh;
+    // the standardised strong block, nS x nS, in shared memory when it fits (hs_cap): every coordinate update
+    // reads one row of it, and from L2 that load was most of the update's latency
+    double *Hs = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(spos + ni) + 15) & ~(uintptr_t)15);
     double *Gb = f.st_d, *Gbs = Gb + ni, *Gxv = Gbs + ni, *Gxm = Gxv + 2 * ni, *Gxs = Gxm + ni,
            *Gvq = Gxs + ni;
     int *Gixx = f.st_i, *Gmm = Gixx + ni, *Gml = Gmm + ni, *Gju = Gml + ni, *Gspos = Gju + ni,
@@ -523,7 +552,7 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
     const double xmz = rd.sums[3 * ni + SU_XMZ], sr_in = rd.sums[3 * ni + SU_SR];
     const int nS = si[SI_NS], ilm = si[SI_ILM];
     const int *hmap = Ggpos;
-    (void)Gspos;
+    const bool in_smem = nS <= hs_cap;
     int nin = si[SI_NIN], nlp = si[SI_NLP];
     double b0 = sd[SD_B0];
     const double al1 = sd[SD_AL], shr = sd[SD_SHR];
@@ -537,6 +566,7 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
         mm[j] = Gmm[j];
         ml[j] = Gml[j];
         hp[j] = hmap[j];
+        spos[j] = Gspos[j];
         g[j] = ok ? (gr[j] - m * sr_in) / s : 0.0;
         hxs[j] = ok ? (hx[j] - m * xmz) / s : 0.0;
         xv[j] = 0.0;
@@ -554,6 +584,7 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
         double *h = H + (size_t)hp[ja] * ldh + hp[jc];
         const double t = (*h - ma * hx[jc] - mc * hx[ja] + ma * mc * xmz) / (Gxs[ja] * Gxs[jc]);
         *h = t;
+        if (in_smem) Hs[(size_t)a * nS + c] = t;
         if (a == c) {  // the curvature xv_j = sum v x_j^2 of the standardised column
             xv[ja] = t;
             Gxv[ja] = t;
@@ -589,10 +620,15 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
                     ml[nin - 1] = k;
                 }
             }
-            const double *hk = H + (size_t)hp[k] * ldh;
-            for (int c = tid; c < nS; c += T) {
-                const int jj = sl[c];
-                g[jj] -= d * hk[hp[jj]];
+            if (in_smem) {
+                const double *hr = Hs + (size_t)spos[k] * nS;
+                for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hr[c];
+            } else {
+                const double *hk = H + (size_t)hp[k] * ldh;
+                for (int c = tid; c < nS; c += T) {
+                    const int jj = sl[c];
+                    g[jj] -= d * hk[hp[jj]];
+                }
             }
             __syncthreads();
         }
@@ -626,10 +662,15 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
                 sr -= d * hxs[k];
                 __syncthreads();
                 if (tid == 0) b[k] = bn;
-                const double *hk = H + (size_t)hp[k] * ldh;
-                for (int c = tid; c < nS; c += T) {
-                    const int jj = sl[c];
-                    g[jj] -= d * hk[hp[jj]];
+                if (in_smem) {
+                    const double *hr = Hs + (size_t)spos[k] * nS;
+                    for (int c = tid; c < nS; c += T) g[sl[c]] -= d * hr[c];
+                } else {
+                    const double *hk = H + (size_t)hp[k] * ldh;
+                    for (int c = tid; c < nS; c += T) {
+                        const int jj = sl[c];
+                        g[jj] -= d * hk[hp[jj]];
+                    }
                 }
                 __syncthreads();
             }
@@ -688,77 +729,81 @@ lognet_solve_kernel(const LognetFit *__restrict__ fits, const RoundDev *__restri
 }
 
 // ---- held-out binomial deviance of a CV fit at every lambda ---------------------------------
-// rows = the fit's hole (its held-out inner fold).  grid.y = chunks of LC lambdas.
-template <int ITER>
+// rows = the fit's hole (its held-out inner fold).  grid.y = chunks of LC lambdas (LC a multiple of 8).
+// eta of eight rows at eight lambdas is one 8 x 8 DMMA accumulation over the columns: A = the rows (read
+// straight from the design, one 32-byte sector per row and step), B = the coefficients of the chunk in shared
+// memory (row stride nip = 4 mod 16 doubles).  A warp takes eight rows at a time; lane (g, k4) then holds
+// eta of row g at lambdas 8 n + 2 k4 + {0, 1} and evaluates their deviance terms -- every lane busy, where
+// the one-row-per-warp form spent a warp reduction per (row, lambda).
+template <int NT>  // lambda tiles per chunk: LC = 8 NT (compile-time: a guarded mma.sync pays a re-convergence each)
 __global__ void __launch_bounds__(256)
-lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, int LC,
+lognet_cvdev_kernel(const LognetFit *__restrict__ fits, int fid, int nip,
                     double *__restrict__ partials /*[gridDim.x][nlam]*/) {
+    constexpr int LC = 8 * NT;
     const LognetFit f = fits[fid];
     const double *X = f.X;
     const long long ld = f.ld;
-    extern __shared__ double sm[];  // beta chunk [LC][ni] + a0[LC] + red [warps][LC]
+    extern __shared__ double sm[];  // beta chunk [LC][nip] + a0[LC] + red [warps][LC]
     const int ni = f.ni;
     const int lmu = fit_scal_i(f)[SI_LMU];
     const int m0 = blockIdx.y * LC;
     const int mc = max(0, min(LC, lmu - m0));
-    double *sb = sm, *sa0 = sb + (size_t)LC * ni, *sred = sa0 + LC;
+    double *sb = sm, *sa0 = sb + (size_t)LC * nip, *sred = sa0 + LC;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    for (int e = threadIdx.x; e < mc * ni; e += blockDim.x) sb[e] = f.beta[(size_t)m0 * ni + e];
-    for (int e = threadIdx.x; e < mc; e += blockDim.x) sa0[e] = f.a0[m0 + e];
+    const int g = lane >> 2, k4 = lane & 3;
+    for (int e = threadIdx.x; e < LC * nip; e += blockDim.x) {
+        const int m = e / nip, c = e - m * nip;
+        sb[e] = (m < mc && c < ni) ? f.beta[(size_t)(m0 + m) * ni + c] : 0.0;  // zero beyond ni: the columns there (w, y, 1) drop out
+    }
+    for (int e = threadIdx.x; e < LC; e += blockDim.x) sa0[e] = e < mc ? f.a0[m0 + e] : 0.0;
     __syncthreads();
-    double acc0 = 0.0, acc1 = 0.0;  // lane l accumulates lambdas l and l + 32 of the chunk
-    const long long wstride = (long long)gridDim.x * nw;
-    for (long long t = (long long)blockIdx.x * nw + wid; t < f.hole_len; t += wstride) {
-        const long long pp = f.hole_begin + t;
+    const int nks = (ni + 3) >> 2;  // 4-column steps
+    double dev[NT][2];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) dev[n][0] = dev[n][1] = 0.0;
+    const long long wstride = (long long)gridDim.x * nw * 8;
+    for (long long t8 = ((long long)blockIdx.x * nw + wid) * 8; t8 < f.hole_len; t8 += wstride) {
+        const long long t = t8 + g;
+        const bool valid = t < f.hole_len;
+        const long long pp = f.hole_begin + (valid ? t : t8);  // (a lane without a row re-reads the first one)
         const long long row = f.list ? (long long)__ldg(f.list + pp) : pp;
         const double *xr = X + (size_t)row * (size_t)ld;
-        double x[2 * ITER];
+        double c[NT][2];
 #pragma unroll
-        for (int i = 0; i < ITER; ++i) {
-            const int c = 2 * lane + 64 * i;
-            double2 t2 = make_double2(0.0, 0.0);
-            if (c + 1 < ld) t2 = __ldg(reinterpret_cast<const double2 *>(xr + c));
-            x[2 * i] = c < ni ? t2.x : 0.0;
-            x[2 * i + 1] = c + 1 < ni ? t2.y : 0.0;
+        for (int n = 0; n < NT; ++n) c[n][0] = c[n][1] = 0.0;
+        const double *bp = sb + (size_t)g * nip + k4;
+#pragma unroll 2
+        for (int kk = 0; kk < nks; ++kk) {
+            const double a = __ldg(xr + 4 * kk + k4);
+#pragma unroll
+            for (int n = 0; n < NT; ++n) atk::dmma884(c[n][0], c[n][1], a, bp[(size_t)n * 8 * nip + 4 * kk]);
         }
         const double yi = __ldg(xr + f.iy);
-        // lane l keeps eta of lambdas l and l + 32 of the chunk; the deviance terms are then evaluated by
-        // all lanes at once (one exp / log sequence per 32 lambdas instead of one per lambda)
-        double eta0 = 0.0, eta1 = 0.0;
-        for (int m = 0; m < mc; ++m) {
-            const double *bm = sb + (size_t)m * ni;
-            double dot = 0.0;
 #pragma unroll
-            for (int i = 0; i < ITER; ++i) {
-                const int c = 2 * lane + 64 * i;
-                if (c < ni) dot += x[2 * i] * bm[c];
-                if (c + 1 < ni) dot += x[2 * i + 1] * bm[c + 1];
-            }
-            const double eta = sa0[m] + warp_sum(dot);
-            if ((m & 31) == lane) {
-                if (m < 32)
-                    eta0 = eta;
-                else
-                    eta1 = eta;
-            }
-        }
+        for (int n = 0; n < NT; ++n) {
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-            if (hh * 32 >= mc) break;  // (warp-uniform)
-            const double eta = hh ? eta1 : eta0;
-            double pr = 1.0 / (1.0 + exp(-eta));
-            pr = fmin(fmax(pr, 1.0e-5), 1.0 - 1.0e-5);
-            const double dv = -2.0 * (yi * log(pr) + (1.0 - yi) * log(1.0 - pr));
-            if (lane + 32 * hh < mc) {
-                if (hh)
-                    acc1 += dv;
-                else
-                    acc0 += dv;
+            for (int j = 0; j < 2; ++j) {
+                const int m = 8 * n + 2 * k4 + j;
+                const double eta = sa0[m] + c[n][j];
+                double pr = 1.0 / (1.0 + exp(-eta));
+                pr = fmin(fmax(pr, 1.0e-5), 1.0 - 1.0e-5);
+                const double dv = -2.0 * (yi * log(pr) + (1.0 - yi) * log(1.0 - pr));
+                if (valid && m < mc) dev[n][j] += dv;
             }
         }
     }
-    if (lane < LC) sred[(size_t)wid * LC + lane] = acc0;
-    if (lane + 32 < LC) sred[(size_t)wid * LC + lane + 32] = acc1;
+    // lanes with the same k4 hold the same lambdas for different rows
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            double v = dev[n][j];
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            const int m = 8 * n + 2 * k4 + j;
+            if (g == 0) sred[(size_t)wid * LC + m] = v;
+        }
     __syncthreads();
     for (int m = threadIdx.x; m < mc; m += blockDim.x) {
         double s = 0.0;
@@ -1008,8 +1053,12 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     ATE_LAUNCHED(ctx);
 
     const size_t pre_smem = sizeof(double) * ((size_t)ni + 32) + sizeof(int) * 2 * (size_t)ldh;
-    const size_t cd_smem = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * (4 * (size_t)ni + 3 * (size_t)ldh);
-    if (cd_smem > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
+    const size_t cd_base = sizeof(double) * (5 * (size_t)ni + 32) + sizeof(int) * (5 * (size_t)ni + (size_t)ldh) + 32;
+    if (cd_base > 200 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni too large");
+    // the rest of the SM's shared memory holds the standardised strong block (hs_cap x hs_cap doubles)
+    int hs_cap = (int)sqrt((double)(224 * 1024 - cd_base) / sizeof(double));
+    if (hs_cap > ldh) hs_cap = ldh;
+    const size_t cd_smem = cd_base + sizeof(double) * (size_t)hs_cap * hs_cap;
     if (cd_smem > 48 * 1024)
         ATE_CUDA(ctx, cudaFuncSetAttribute(lognet_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cd_smem));
     int rc = 0;
@@ -1108,7 +1157,7 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
         // is read back while the solve runs, and the next round is planned and enqueued behind the solve
         ATE_CUDA(ctx, cudaMemcpyAsync(hflags, dflags, sizeof(int) * 4 * nfits, cudaMemcpyDeviceToHost, ctx->stream));
         ATE_CUDA(ctx, cudaEventRecord(ev_flags, ctx->stream));
-        lognet_solve_kernel<<<nfits, CD_THREADS, cd_smem, ctx->stream>>>(dfits, drdev);
+        lognet_solve_kernel<<<nfits, CD_THREADS, cd_smem, ctx->stream>>>(dfits, drdev, hs_cap);
         ATE_LAUNCHED(ctx);
         if (timing) { const double t = tnow(); t_host += t - t_mark; t_mark = t; }
         ATE_CUDA(ctx, cudaEventSynchronize(ev_flags));
@@ -1130,26 +1179,38 @@ int ate_i_cv_binomial(ate_ctx *ctx, const double *X, long long ld, int ni, int i
     // ---- held-out deviance of every CV fold at every lambda (this rank's rows of the fold) ----
     std::vector<double> hcv;
     if (F > 0) {
-        int LC = (int)((96 * 1024) / (sizeof(double) * (size_t)ni));
+        const int nip = (ni + 15) / 16 * 16 + 4;  // row stride of the coefficient chunk: 4 mod 16 doubles
+        int LC = (int)((128 * 1024) / (sizeof(double) * (size_t)nip)) / 8 * 8;
         if (LC > 64) LC = 64;
-        if (LC < 1) LC = 1;
+        if (LC < 8) LC = 8;
         const int nchunk = (nlam + LC - 1) / LC;
-        const size_t cv_smem = sizeof(double) * ((size_t)LC * ni + LC + 8 * (size_t)LC);
-        rc = dispatch_iter(ni, [&](auto it) {
-            constexpr int IT = decltype(it)::value;
-            if (cudaFuncSetAttribute(lognet_cvdev_kernel<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cv_smem) != cudaSuccess) return -1;
+        const size_t cv_smem = sizeof(double) * ((size_t)LC * nip + LC + 8 * (size_t)LC);
+        if (cv_smem > 220 * 1024) return ate_fail(ctx, -1, "cv_binomial: ni = %d too large for the cv kernel", ni);
+        auto cv_launch = [&](auto nt_tag, int id, bool size_only) -> int {
+            constexpr int NTt = decltype(nt_tag)::value;
+            if (size_only)
+                return cudaFuncSetAttribute(lognet_cvdev_kernel<NTt>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cv_smem) == cudaSuccess ? 0 : -1;
+            lognet_cvdev_kernel<NTt><<<dim3(ev_blocks, nchunk), 256, cv_smem, ctx->stream>>>(dfits, id, nip, dpart);
             return 0;
-        });
-        if (rc < 0) return ate_fail(ctx, -1, "cv_binomial: cannot size cv kernel");
+        };
+        auto cv_dispatch = [&](int id, bool size_only) -> int {
+            switch (LC / 8) {
+                case 1: return cv_launch(std::integral_constant<int, 1>{}, id, size_only);
+                case 2: return cv_launch(std::integral_constant<int, 2>{}, id, size_only);
+                case 3: return cv_launch(std::integral_constant<int, 3>{}, id, size_only);
+                case 4: return cv_launch(std::integral_constant<int, 4>{}, id, size_only);
+                case 5: return cv_launch(std::integral_constant<int, 5>{}, id, size_only);
+                case 6: return cv_launch(std::integral_constant<int, 6>{}, id, size_only);
+                case 7: return cv_launch(std::integral_constant<int, 7>{}, id, size_only);
+                default: return cv_launch(std::integral_constant<int, 8>{}, id, size_only);
+            }
+        };
+        if (cv_dispatch(0, true) != 0) return ate_fail(ctx, -1, "cv_binomial: cannot size cv kernel");
         ATE_CUDA(ctx, cudaMemsetAsync(dcv, 0, sizeof(double) * (size_t)nfol * nlam, ctx->stream));
         for (int q = 0; q < nfol; ++q) {
             const int id = nlead + q;
             ATE_CUDA(ctx, cudaMemsetAsync(dpart, 0, sizeof(double) * (size_t)ev_blocks * nlam, ctx->stream));
-            dispatch_iter(ni, [&](auto it) {
-                constexpr int IT = decltype(it)::value;
-                lognet_cvdev_kernel<IT><<<dim3(ev_blocks, nchunk), 256, cv_smem, ctx->stream>>>(dfits, id, LC, dpart);
-                return 0;
-            });
+            cv_dispatch(id, false);
             ATE_LAUNCHED(ctx);
             fold_partials_kernel<<<(nlam + 7) / 8, 256, 0, ctx->stream>>>(dpart, ev_blocks, nlam, dcv + (size_t)q * nlam);
             ATE_LAUNCHED(ctx);
